@@ -1,0 +1,143 @@
+/* madmom_b200.h -- C ABI of libmadmom_b200.so, the sm_100a spectral front end behind madmom's Processor API.
+ *
+ * The reference (CPJKU/madmom) has no FFI on this path: it is numpy/scipy all the way down.  Each entry
+ * point therefore replaces a *Python* call site of the reference; INTEGRATION.md shows the ctypes binding a
+ * madmom maintainer would add.  What is replaced, per plan field:
+ *
+ *   framing      FramedSignal.__init__ / signal_frame            madmom/audio/signal.py:1103-1156, 860-962
+ *   window+FFT   ShortTimeFourierTransform.__new__ / stft()      madmom/audio/stft.py:317-373, 49-133
+ *   magnitude    Spectrogram.__new__ (np.abs)                    madmom/audio/spectrogram.py:122-141
+ *   filterbank   FilteredSpectrogram.__new__ (np.dot)            madmom/audio/spectrogram.py:363-390
+ *   log          LogarithmicSpectrogram.__new__                  madmom/audio/spectrogram.py:519-544
+ *   difference   SpectrogramDifference.__new__ / ...Processor    madmom/audio/spectrogram.py:960-1004, 1085-1139
+ *   flux         spectral_flux / superflux (row sum)             madmom/features/onsets.py:163-240
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
+ * MMB_E_* code and never throws or aborts; the message of the last failure on the calling thread is
+ * available from mmb_last_error().  Device buffers (PCM in, features out) are owned by the caller; the
+ * library owns only plan constants (window, twiddles, filterbank) and layout tables.  mmb_run() enqueues
+ * work on the caller's stream and does not synchronise.
+ */
+#ifndef MADMOM_B200_H
+#define MADMOM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MMB_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define MMB_API __attribute__((visibility("default")))
+#else
+#define MMB_API
+#endif
+
+enum {
+  MMB_OK = 0,
+  MMB_E_INVALID = -1,     /* bad argument (the Python layer raises ValueError / TypeError before this) */
+  MMB_E_UNSUPPORTED = -2, /* valid for the reference but not implemented here (NotImplementedError)   */
+  MMB_E_CUDA = -3,        /* CUDA runtime failure; message carries cudaGetErrorString                 */
+  MMB_E_NOMEM = -4
+};
+
+enum { MMB_PCM_I16 = 0, MMB_PCM_F32 = 1 };
+enum { MMB_LOG_NONE = 0, MMB_LOG_LOG10 = 1, MMB_LOG_MULADD = 2 };
+
+typedef struct mmb_plan mmb_plan;     /* immutable after creation, usable from any host thread */
+typedef struct mmb_layout mmb_layout; /* device-resident description of a batch of units         */
+
+/* One recipe = one fused kernel configuration. */
+typedef struct mmb_config {
+  int32_t frame_size;      /* 1024, 2048 or 4096 (FramedSignalProcessor.frame_size); fft_size == frame_size */
+  int32_t pcm_dtype;       /* MMB_PCM_I16 / MMB_PCM_F32 (Signal dtype)                                      */
+  double hop_size;         /* samples between frames, may be fractional (sample_rate / fps)                 */
+  int32_t origin;          /* integer origin, literals already resolved (signal.py:1126-1142)               */
+  int32_t circular_shift;  /* STFT circular_shift flag (stft.py:106-119)                                    */
+  const double* fft_window;/* frame_size float64 values actually multiplied onto the samples, i.e.
+                              window / iinfo(dtype).max for integer PCM (stft.py:331-349)                   */
+  /* filterbank as one contiguous run of non-zero weights per band (Filterbank (K x B) float32 columns) */
+  int32_t num_bands;       /* 0: no filterbank stage; only stft / spec outputs are available               */
+  const int32_t* band_start; /* [num_bands] first non-zero bin                                             */
+  const int32_t* band_len;   /* [num_bands] run length                                                     */
+  const float* band_weights; /* concatenated runs                                                          */
+  int32_t log_mode;        /* MMB_LOG_*: none / log10(x*mul+add) / x*mul+add                               */
+  float mul, add;
+  int32_t diff_frames;     /* d >= 1 (from _diff_frames, spectrogram.py:834-864), 0: no difference stage   */
+  int32_t diff_max_bins;   /* frequency maximum-filter width (<= 1: none), scipy 'reflect' borders         */
+  int32_t positive_diffs;
+  int32_t chunk_frames;    /* output frames per work chunk, 0 = library default                            */
+  int32_t device;          /* CUDA device ordinal                                                          */
+} mmb_config;
+
+/* One independent unit of work: a whole track (sample_base = frame_first = 0, pcm_len = num_samples) or a
+ * frame range of a long signal with its PCM halo (FramedSignal.__getitem__(slice), signal.py:1181-1194).
+ * Frame g of the unit's signal starts at sample int(g * hop) - frame_size/2 - origin; samples outside
+ * [sample_base, sample_base + pcm_len) read as zero. */
+typedef struct mmb_track {
+  int64_t pcm_offset;  /* element offset of the unit's first local sample in the PCM buffer */
+  int64_t pcm_len;     /* local samples                                                     */
+  int64_t sample_base; /* global sample index of local sample 0                             */
+  int64_t frame_first; /* global index of the first output frame                            */
+  int64_t frame_count; /* output rows                                                       */
+  int64_t out_row;     /* first output row                                                  */
+} mmb_track;
+
+/* Output matrices, row-major, leading dimensions in ELEMENTS; a null pointer disables that output.
+ * hstack((spec, diff)) of SpectrogramDifferenceProcessor(stack_diffs=np.hstack) is log = base,
+ * diff = base + num_bands, both with ld = row length of the stacked matrix. */
+typedef struct mmb_outputs {
+  void* stft;  int64_t ld_stft;  /* complex64 (rows, frame_size/2)              */
+  float* spec; int64_t ld_spec;  /* magnitudes (rows, frame_size/2)             */
+  float* filt; int64_t ld_filt;  /* filtered, before log (rows, num_bands)      */
+  float* log;  int64_t ld_log;   /* log-filtered spectrogram (rows, num_bands)  */
+  float* diff; int64_t ld_diff;  /* (positive, max-filtered) difference         */
+  float* odf;                    /* row sums of diff (rows)                     */
+} mmb_outputs;
+
+typedef struct mmb_plan_info {
+  int32_t frame_size, num_bins, num_bands, chunk_frames;
+  int32_t smem_bytes, ctas_per_sm, num_sms, frames_per_round;
+} mmb_plan_info;
+
+MMB_API int mmb_version(void);
+MMB_API const char* mmb_last_error(void);
+
+/* integer framing helpers (bit-exact with signal.py:1145-1156 and :917-919) */
+MMB_API int64_t mmb_num_frames(int64_t num_samples, double hop_size, int32_t end_extend);
+MMB_API int64_t mmb_frame_start(int64_t index, int32_t frame_size, double hop_size, int32_t origin);
+
+MMB_API int mmb_plan_create(const mmb_config* cfg, mmb_plan** out);
+MMB_API int mmb_plan_destroy(mmb_plan* plan);
+MMB_API int mmb_plan_get_info(const mmb_plan* plan, mmb_plan_info* info);
+
+/* Upload the unit table of a batch (host array of n units) and build the chunk index. */
+MMB_API int mmb_layout_create(const mmb_plan* plan, const mmb_track* units, int32_t n_units, mmb_layout** out);
+MMB_API int mmb_layout_destroy(mmb_layout* layout);
+
+/* Device path: pcm_dev and every non-null output are DEVICE pointers; asynchronous on `stream`
+ * (a cudaStream_t passed as void*).  *launches (optional) receives the number of kernels launched. */
+MMB_API int mmb_run(const mmb_plan* plan, const mmb_layout* layout, const void* pcm_dev, const mmb_outputs* outs,
+            void* stream, int32_t* launches);
+
+/* Host path (what a madmom call site holding numpy arrays uses): pcm_host and the outputs are HOST
+ * pointers (pinned for full speed); the library stages units through its own device buffers with
+ * host-to-device copy, kernel and device-to-host copy overlapped on three streams, and returns when the
+ * outputs are complete.  `units` is the same host table given to a layout (out_row / pcm_offset global). */
+MMB_API int mmb_run_host(const mmb_plan* plan, const mmb_track* units, int32_t n_units, const void* pcm_host,
+                 const mmb_outputs* outs_host, int32_t* launches);
+
+/* pinned host memory for mmb_run_host callers without their own allocator */
+MMB_API int mmb_host_alloc(void** ptr, int64_t bytes);
+MMB_API int mmb_host_free(void* ptr);
+
+/* Calibration: measured FP32 FMA throughput of `device` in TFLOP/s (dependent FFMA chains on every SM,
+ * best of 5, CUDA events).  The front end is FP32-pipe bound; bench.py reports its roofline against this. */
+MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MADMOM_B200_H */

@@ -1,0 +1,289 @@
+"""ctypes binding of libmadmom_b200.so (include/madmom_b200.h) and the thin `FrontEndPlan` wrapper used by
+the processor classes.  There is no fallback: if the library cannot be loaded every compute call raises."""
+import ctypes
+import os
+import threading
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIBPATH = os.path.join(_HERE, "lib", "libmadmom_b200.so")
+
+MMB_OK, MMB_E_INVALID, MMB_E_UNSUPPORTED, MMB_E_CUDA, MMB_E_NOMEM = 0, -1, -2, -3, -4
+PCM_I16, PCM_F32 = 0, 1
+LOG_NONE, LOG_LOG10, LOG_MULADD = 0, 1, 2
+
+c_i32, c_i64, c_f32, c_f64, c_vp = ctypes.c_int32, ctypes.c_int64, ctypes.c_float, ctypes.c_double, ctypes.c_void_p
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("frame_size", c_i32), ("pcm_dtype", c_i32), ("hop_size", c_f64), ("origin", c_i32),
+                ("circular_shift", c_i32), ("fft_window", ctypes.POINTER(c_f64)),
+                ("num_bands", c_i32), ("band_start", ctypes.POINTER(c_i32)), ("band_len", ctypes.POINTER(c_i32)),
+                ("band_weights", ctypes.POINTER(c_f32)), ("log_mode", c_i32), ("mul", c_f32), ("add", c_f32),
+                ("diff_frames", c_i32), ("diff_max_bins", c_i32), ("positive_diffs", c_i32),
+                ("chunk_frames", c_i32), ("device", c_i32)]
+
+
+class Track(ctypes.Structure):
+    _fields_ = [("pcm_offset", c_i64), ("pcm_len", c_i64), ("sample_base", c_i64), ("frame_first", c_i64),
+                ("frame_count", c_i64), ("out_row", c_i64)]
+
+
+TRACK_DTYPE = np.dtype([("pcm_offset", "<i8"), ("pcm_len", "<i8"), ("sample_base", "<i8"), ("frame_first", "<i8"),
+                        ("frame_count", "<i8"), ("out_row", "<i8")])
+
+
+class Outputs(ctypes.Structure):
+    _fields_ = [("stft", c_vp), ("ld_stft", c_i64), ("spec", c_vp), ("ld_spec", c_i64), ("filt", c_vp),
+                ("ld_filt", c_i64), ("log", c_vp), ("ld_log", c_i64), ("diff", c_vp), ("ld_diff", c_i64),
+                ("odf", c_vp)]
+
+
+class PlanInfo(ctypes.Structure):
+    _fields_ = [(n, c_i32) for n in ("frame_size", "num_bins", "num_bands", "chunk_frames", "smem_bytes",
+                                     "ctas_per_sm", "num_sms", "frames_per_round")]
+
+
+EXPORTS = {
+    "mmb_version": (c_i32, []),
+    "mmb_last_error": (ctypes.c_char_p, []),
+    "mmb_num_frames": (c_i64, [c_i64, c_f64, c_i32]),
+    "mmb_frame_start": (c_i64, [c_i64, c_i32, c_f64, c_i32]),
+    "mmb_plan_create": (c_i32, [ctypes.POINTER(Config), ctypes.POINTER(c_vp)]),
+    "mmb_plan_destroy": (c_i32, [c_vp]),
+    "mmb_plan_get_info": (c_i32, [c_vp, ctypes.POINTER(PlanInfo)]),
+    "mmb_layout_create": (c_i32, [c_vp, c_vp, c_i32, ctypes.POINTER(c_vp)]),
+    "mmb_layout_destroy": (c_i32, [c_vp]),
+    "mmb_run": (c_i32, [c_vp, c_vp, c_vp, ctypes.POINTER(Outputs), c_vp, ctypes.POINTER(c_i32)]),
+    "mmb_run_host": (c_i32, [c_vp, c_vp, c_i32, c_vp, ctypes.POINTER(Outputs), ctypes.POINTER(c_i32)]),
+    "mmb_host_alloc": (c_i32, [ctypes.POINTER(c_vp), c_i64]),
+    "mmb_host_free": (c_i32, [c_vp]),
+    "mmb_measure_fp32_peak": (c_i32, [c_i32, ctypes.POINTER(c_f64)]),
+}
+
+_lib = None
+_lock = threading.Lock()
+launch_count = 0          # kernels launched through this binding (bench.py reports it as gpu_launches)
+
+
+class LibraryError(RuntimeError):
+    pass
+
+
+def load():
+    """Load the shared library (once).  Raises LibraryError if it is missing -- there is no CPU path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIBPATH):
+            raise LibraryError("%s not found: build it with `python -m madmom_b200.build` "
+                               "(madmom_b200 has no CPU fallback)" % LIBPATH)
+        lib = ctypes.CDLL(LIBPATH)
+        for name, (res, args) in EXPORTS.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def _check(rc):
+    if rc == MMB_OK:
+        return
+    msg = load().mmb_last_error().decode("utf-8", "replace")
+    if rc == MMB_E_UNSUPPORTED:
+        raise NotImplementedError(msg)
+    if rc == MMB_E_INVALID:
+        raise ValueError(msg)
+    if rc == MMB_E_NOMEM:
+        raise MemoryError(msg)
+    raise LibraryError("libmadmom_b200: %s (code %d)" % (msg, rc))
+
+
+def num_frames(num_samples, hop_size, end="normal"):
+    if end not in ("normal", "extend"):
+        raise ValueError("end of signal handling '%s' unknown" % end)
+    return int(load().mmb_num_frames(int(num_samples), float(hop_size), 1 if end == "extend" else 0))
+
+
+def frame_start(index, frame_size, hop_size, origin=0):
+    return int(load().mmb_frame_start(int(index), int(frame_size), float(hop_size), int(origin)))
+
+
+def measure_fp32_peak(device=0):
+    """Measured FP32 FMA peak of the device in TFLOP/s (mmb_measure_fp32_peak)."""
+    v = c_f64(0.0)
+    _check(load().mmb_measure_fp32_peak(int(device), ctypes.byref(v)))
+    return v.value
+
+
+def compact_filterbank(fb):
+    """(K, B) dense float32 filterbank -> (start[B], len[B], weights[nnz]): one run min..max nonzero per band."""
+    fb = np.asarray(fb, dtype=np.float32)
+    starts, lens, ws = [], [], []
+    for b in range(fb.shape[1]):
+        nz = np.nonzero(fb[:, b])[0]
+        if len(nz) == 0:
+            starts.append(0), lens.append(0)
+            continue
+        s, e = int(nz[0]), int(nz[-1]) + 1
+        starts.append(s), lens.append(e - s), ws.append(fb[s:e, b])
+    w = np.concatenate(ws).astype(np.float32) if ws else np.zeros(0, np.float32)
+    return np.asarray(starts, np.int32), np.asarray(lens, np.int32), np.ascontiguousarray(w)
+
+
+def make_units(num_samples, frame_counts, pcm_offsets=None, sample_base=None, frame_first=None):
+    """Unit table for whole tracks laid back to back (or explicit offsets)."""
+    num_samples = np.asarray(num_samples, dtype=np.int64)
+    frame_counts = np.asarray(frame_counts, dtype=np.int64)
+    n = len(num_samples)
+    u = np.zeros(n, dtype=TRACK_DTYPE)
+    u["pcm_len"] = num_samples
+    u["pcm_offset"] = np.concatenate(([0], np.cumsum(num_samples)[:-1])) if pcm_offsets is None else pcm_offsets
+    u["sample_base"] = 0 if sample_base is None else sample_base
+    u["frame_first"] = 0 if frame_first is None else frame_first
+    u["frame_count"] = frame_counts
+    u["out_row"] = np.concatenate(([0], np.cumsum(frame_counts)[:-1]))
+    return u
+
+
+OUTPUT_NAMES = ("stft", "spec", "filt", "log", "diff", "odf")
+
+
+class FrontEndPlan(object):
+    """One fused-kernel recipe (mmb_plan).  `filterbank` is a dense (K, B) array or None."""
+
+    def __init__(self, frame_size, hop_size, fft_window, pcm_dtype=np.int16, origin=0, circular_shift=False,
+                 filterbank=None, log_mode=LOG_NONE, mul=1.0, add=0.0, diff_frames=0, diff_max_bins=0,
+                 positive_diffs=False, chunk_frames=0, device=0):
+        lib = load()
+        self._lib = lib
+        self._handle = c_vp()
+        self._layouts = {}
+        self.frame_size, self.hop_size, self.origin = int(frame_size), float(hop_size), int(origin)
+        self.num_bins = self.frame_size // 2
+        self.device = int(device)
+        pcm_dtype = np.dtype(pcm_dtype)
+        if pcm_dtype == np.int16:
+            code = PCM_I16
+        elif pcm_dtype == np.float32:
+            code = PCM_F32
+        else:
+            raise NotImplementedError("PCM dtype %s not supported on the GPU path (int16 or float32)" % pcm_dtype)
+        self.pcm_dtype = pcm_dtype
+        win = np.ascontiguousarray(np.asarray(fft_window, dtype=np.float64))
+        if win.shape != (self.frame_size,):
+            raise ValueError("fft_window must have frame_size elements")
+        cfg = Config()
+        cfg.frame_size, cfg.pcm_dtype, cfg.hop_size, cfg.origin = self.frame_size, code, self.hop_size, self.origin
+        cfg.circular_shift = int(bool(circular_shift))
+        cfg.fft_window = win.ctypes.data_as(ctypes.POINTER(c_f64))
+        keep = [win]
+        if filterbank is not None:
+            s, l, w = compact_filterbank(filterbank)
+            keep += [s, l, w]
+            cfg.num_bands = len(s)
+            cfg.band_start = s.ctypes.data_as(ctypes.POINTER(c_i32))
+            cfg.band_len = l.ctypes.data_as(ctypes.POINTER(c_i32))
+            cfg.band_weights = w.ctypes.data_as(ctypes.POINTER(c_f32))
+        self.num_bands = int(cfg.num_bands)
+        cfg.log_mode, cfg.mul, cfg.add = int(log_mode), float(mul), float(add)
+        cfg.diff_frames, cfg.diff_max_bins = int(diff_frames), int(diff_max_bins or 0)
+        cfg.positive_diffs, cfg.chunk_frames, cfg.device = int(bool(positive_diffs)), int(chunk_frames), self.device
+        self.diff_frames = int(diff_frames)
+        _check(lib.mmb_plan_create(ctypes.byref(cfg), ctypes.byref(self._handle)))
+        info = PlanInfo()
+        _check(lib.mmb_plan_get_info(self._handle, ctypes.byref(info)))
+        self.info = {n: getattr(info, n) for n, _ in PlanInfo._fields_}
+
+    def __del__(self):
+        try:
+            for h in self._layouts.values():
+                self._lib.mmb_layout_destroy(h)
+            if self._handle:
+                self._lib.mmb_plan_destroy(self._handle)
+        except Exception:
+            pass
+
+    def width(self, name):
+        return {"stft": self.num_bins, "spec": self.num_bins, "odf": 1}.get(name, self.num_bands)
+
+    def _layout(self, units):
+        key = units.tobytes()
+        h = self._layouts.get(key)
+        if h is None:
+            if len(self._layouts) > 16:
+                for old in self._layouts.values():
+                    self._lib.mmb_layout_destroy(old)
+                self._layouts.clear()
+            h = c_vp()
+            _check(self._lib.mmb_layout_create(self._handle, units.ctypes.data_as(c_vp), len(units), ctypes.byref(h)))
+            self._layouts[key] = h
+        return h
+
+    @staticmethod
+    def _fill(outs, ptrs):
+        o = Outputs()
+        for name, (ptr, ld) in ptrs.items():
+            setattr(o, name, ptr)
+            if name != "odf":
+                setattr(o, "ld_" + name, ld)
+        return o
+
+    def run(self, pcm, units, outputs, stream=None):
+        """Device path.  pcm: CUDA tensor; outputs: {name: CUDA tensor (rows, >= width) or column view}.
+        Asynchronous on the current torch stream."""
+        global launch_count
+        import torch
+        units = np.ascontiguousarray(units, dtype=TRACK_DTYPE)
+        if not pcm.is_cuda or pcm.device.index != self.device:
+            raise ValueError("pcm must live on cuda:%d" % self.device)
+        want = torch.int16 if self.pcm_dtype == np.int16 else torch.float32
+        if pcm.dtype != want or not pcm.is_contiguous():
+            raise ValueError("pcm must be a contiguous %s tensor" % want)
+        ptrs = {}
+        for name, t in outputs.items():
+            if name not in OUTPUT_NAMES:
+                raise ValueError("unknown output %r" % name)
+            if t.dtype != (torch.complex64 if name == "stft" else torch.float32) or not t.is_cuda:
+                raise ValueError("output %s has the wrong dtype/device" % name)
+            if name == "odf":
+                if not t.is_contiguous():
+                    raise ValueError("odf output must be contiguous")
+                ptrs[name] = (t.data_ptr(), 1)
+            else:
+                if t.dim() != 2 or t.stride(1) != 1 or t.shape[1] != self.width(name):
+                    raise ValueError("output %s must be (rows, %d) with unit column stride" % (name, self.width(name)))
+                ptrs[name] = (t.data_ptr(), t.stride(0))
+        o = self._fill(outputs, ptrs)
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        n = c_i32(0)
+        _check(self._lib.mmb_run(self._handle, self._layout(units), pcm.data_ptr(), ctypes.byref(o), stream,
+                                 ctypes.byref(n)))
+        launch_count += n.value
+        return n.value
+
+    def run_host(self, pcm, units, outputs):
+        """Host path (mmb_run_host).  pcm: contiguous numpy array or CPU tensor; outputs: {name: numpy array
+        or CPU tensor}; returns when the outputs are complete."""
+        global launch_count
+        units = np.ascontiguousarray(units, dtype=TRACK_DTYPE)
+
+        def addr(a):
+            return a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data
+
+        def strides(a):
+            if hasattr(a, "data_ptr"):
+                return a.stride(0) if a.dim() == 2 else 1
+            return a.strides[0] // a.itemsize if a.ndim == 2 else 1
+        ptrs = {name: (addr(a), strides(a)) for name, a in outputs.items()}
+        o = self._fill(outputs, ptrs)
+        n = c_i32(0)
+        _check(self._lib.mmb_run_host(self._handle, units.ctypes.data_as(c_vp), len(units), addr(pcm),
+                                      ctypes.byref(o), ctypes.byref(n)))
+        launch_count += n.value
+        return n.value

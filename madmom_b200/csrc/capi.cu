@@ -1,0 +1,419 @@
+// C ABI of libmadmom_b200.so (see include/madmom_b200.h).  Host-side plan construction: twiddle tables
+// are generated in float64 and rounded once to float32; the fft_window is scaled by 0.5 (exact) because
+// the kernel's real-FFT split omits that factor.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/madmom_b200.h"
+#include "frontend_params.h"
+
+using mmb::FrontendParams;
+using mmb::Track;
+
+static_assert(sizeof(mmb_track) == sizeof(Track), "mmb_track layout");
+
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static int cuda_fail(cudaError_t e, const char* what) {
+  return fail(MMB_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
+
+struct mmb_plan {
+  mmb_config cfg;
+  int num_sms = 0;
+  int nnz = 0;
+  int span_cap = 0;
+  int sample_bytes = 2;
+  int smem_bytes = 0;
+  int ctas_per_sm = 0;
+  int chunk_frames = 0;
+  float* d_win = nullptr;
+  float2 *d_tw1 = nullptr, *d_tw2k = nullptr, *d_tw4k = nullptr;
+  int32_t *d_bstart = nullptr, *d_blen = nullptr, *d_bwoff = nullptr;
+  float* d_w = nullptr;
+};
+
+struct mmb_layout {
+  Track* d_tracks = nullptr;
+  int32_t* d_prefix = nullptr;
+  int32_t n = 0;
+  int32_t total_chunks = 0;
+  int64_t total_rows = 0;
+};
+
+extern "C" int mmb_version(void) { return MMB_VERSION; }
+extern "C" const char* mmb_last_error(void) { return g_err.c_str(); }
+
+extern "C" int64_t mmb_num_frames(int64_t num_samples, double hop_size, int32_t end_extend) {
+  // np.ceil(len / hop) ('normal') or np.floor(len / hop + 1) ('extend'), float64 (signal.py:1145-1156)
+  const double q = (double)num_samples / hop_size;
+  return end_extend ? (int64_t)std::floor(q + 1.0) : (int64_t)std::ceil(q);
+}
+
+extern "C" int64_t mmb_frame_start(int64_t index, int32_t frame_size, double hop_size, int32_t origin) {
+  return (int64_t)((double)index * hop_size) - (int64_t)(frame_size / 2) - (int64_t)origin;
+}
+
+template <typename T>
+static cudaError_t upload(T** dst, const std::vector<T>& src) {
+  *dst = nullptr;
+  if (src.empty()) return cudaSuccess;
+  cudaError_t e = cudaMalloc((void**)dst, src.size() * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+extern "C" int mmb_plan_destroy(mmb_plan* p) {
+  if (!p) return MMB_OK;
+  cudaFree(p->d_win); cudaFree(p->d_tw1); cudaFree(p->d_tw2k); cudaFree(p->d_tw4k);
+  cudaFree(p->d_bstart); cudaFree(p->d_blen); cudaFree(p->d_bwoff); cudaFree(p->d_w);
+  delete p;
+  return MMB_OK;
+}
+
+extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
+  if (!cfg || !out) return fail(MMB_E_INVALID, "null argument");
+  *out = nullptr;
+  const int N = cfg->frame_size;
+  if (N != 1024 && N != 2048 && N != 4096)
+    return fail(MMB_E_UNSUPPORTED, "frame_size must be 1024, 2048 or 4096");
+  if (cfg->pcm_dtype != MMB_PCM_I16 && cfg->pcm_dtype != MMB_PCM_F32)
+    return fail(MMB_E_INVALID, "pcm_dtype must be MMB_PCM_I16 or MMB_PCM_F32");
+  if (!(cfg->hop_size > 0.0) || !std::isfinite(cfg->hop_size)) return fail(MMB_E_INVALID, "hop_size must be > 0");
+  if (!cfg->fft_window) return fail(MMB_E_INVALID, "fft_window is null");
+  if (cfg->num_bands < 0) return fail(MMB_E_INVALID, "num_bands < 0");
+  if (cfg->num_bands > 0 && (!cfg->band_start || !cfg->band_len || !cfg->band_weights))
+    return fail(MMB_E_INVALID, "filterbank arrays are null");
+  if (cfg->diff_frames < 0 || cfg->diff_frames > mmb::kMaxDiffFrames)
+    return fail(MMB_E_UNSUPPORTED, "diff_frames must be in [0, 16]");
+  if (cfg->log_mode < 0 || cfg->log_mode > 2) return fail(MMB_E_INVALID, "bad log_mode");
+  const int K = N / 2;
+  std::vector<int32_t> woff(cfg->num_bands);
+  int nnz = 0;
+  for (int b = 0; b < cfg->num_bands; ++b) {
+    if (cfg->band_start[b] < 0 || cfg->band_len[b] < 0 || cfg->band_start[b] + cfg->band_len[b] > K)
+      return fail(MMB_E_INVALID, "filterbank band outside [0, frame_size/2)");
+    woff[b] = nnz;
+    nnz += cfg->band_len[b];
+  }
+  mmb_plan* p = new (std::nothrow) mmb_plan();
+  if (!p) return fail(MMB_E_NOMEM, "out of host memory");
+  p->cfg = *cfg;
+  p->cfg.fft_window = nullptr; p->cfg.band_start = nullptr; p->cfg.band_len = nullptr; p->cfg.band_weights = nullptr;
+  p->nnz = nnz;
+  p->sample_bytes = cfg->pcm_dtype == MMB_PCM_I16 ? 2 : 4;
+  cudaError_t e = cudaSetDevice(cfg->device);
+  if (e != cudaSuccess) { delete p; return cuda_fail(e, "cudaSetDevice"); }
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, cfg->device);
+  if (e != cudaSuccess) { delete p; return cuda_fail(e, "cudaGetDeviceProperties"); }
+  p->num_sms = prop.multiProcessorCount;
+
+  // ---- tables (float64 -> float32)
+  const double PI = 3.14159265358979323846264338327950288;
+  std::vector<float> win(N);
+  for (int i = 0; i < N; ++i) win[i] = (float)(0.5 * cfg->fft_window[i]);
+  std::vector<float2> tw1(1024), tw2k(1024), tw4k(512);
+  for (int k1 = 0; k1 < 32; ++k1)
+    for (int l = 0; l < 32; ++l) {
+      const double a = -2.0 * PI * (double)((l * k1) % 1024) / 1024.0;
+      tw1[k1 * 32 + l] = make_float2((float)std::cos(a), (float)std::sin(a));
+    }
+  for (int k = 0; k < 1024; ++k) {
+    const double a = -2.0 * PI * (double)k / 2048.0;
+    tw2k[k] = make_float2((float)std::cos(a), (float)std::sin(a));
+  }
+  for (int j = 0; j < 512; ++j) {
+    const double a = -2.0 * PI * (double)(2 * j + 1) / 4096.0;
+    tw4k[j] = make_float2((float)std::cos(a), (float)std::sin(a));
+  }
+  std::vector<int32_t> bstart(cfg->band_start, cfg->band_start + cfg->num_bands);
+  std::vector<int32_t> blen(cfg->band_len, cfg->band_len + cfg->num_bands);
+  std::vector<float> w(cfg->band_weights, cfg->band_weights + nnz);
+  if ((e = upload(&p->d_win, win)) != cudaSuccess || (e = upload(&p->d_tw1, tw1)) != cudaSuccess ||
+      (e = upload(&p->d_tw2k, tw2k)) != cudaSuccess || (e = upload(&p->d_tw4k, tw4k)) != cudaSuccess ||
+      (e = upload(&p->d_bstart, bstart)) != cudaSuccess || (e = upload(&p->d_blen, blen)) != cudaSuccess ||
+      (e = upload(&p->d_bwoff, woff)) != cudaSuccess || (e = upload(&p->d_w, w)) != cudaSuccess) {
+    mmb_plan_destroy(p);
+    return cuda_fail(e, "plan constant upload");
+  }
+  // ---- shared-memory budget: the staged PCM span of one round
+  const int fpr = mmb::frames_per_round(N);
+  p->span_cap = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N) + 7) & ~7;
+  const mmb::SmemLayout L = mmb::smem_layout(N, cfg->num_bands, nnz, p->span_cap, p->sample_bytes);
+  p->smem_bytes = L.total;
+  if (p->smem_bytes > (int)prop.sharedMemPerBlockOptin) {
+    mmb_plan_destroy(p);
+    return fail(MMB_E_UNSUPPORTED, "configuration needs more shared memory than one SM has (hop_size or filterbank too large)");
+  }
+  e = mmb::frontend_max_ctas_per_sm(N, p->sample_bytes, p->smem_bytes, &p->ctas_per_sm);
+  if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "occupancy query"); }
+  if (p->ctas_per_sm < 1) { mmb_plan_destroy(p); return fail(MMB_E_UNSUPPORTED, "kernel does not fit on an SM"); }
+  p->chunk_frames = cfg->chunk_frames > 0 ? cfg->chunk_frames : 32 * fpr - cfg->diff_frames;
+  *out = p;
+  return MMB_OK;
+}
+
+extern "C" int mmb_plan_get_info(const mmb_plan* p, mmb_plan_info* info) {
+  if (!p || !info) return fail(MMB_E_INVALID, "null argument");
+  info->frame_size = p->cfg.frame_size; info->num_bins = p->cfg.frame_size / 2; info->num_bands = p->cfg.num_bands;
+  info->chunk_frames = p->chunk_frames; info->smem_bytes = p->smem_bytes; info->ctas_per_sm = p->ctas_per_sm;
+  info->num_sms = p->num_sms; info->frames_per_round = mmb::frames_per_round(p->cfg.frame_size);
+  return MMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ layouts
+static int validate_units(const mmb_track* u, int32_t n) {
+  if (!u || n <= 0) return fail(MMB_E_INVALID, "no units");
+  for (int32_t i = 0; i < n; ++i) {
+    if (u[i].pcm_offset < 0 || u[i].pcm_len < 0 || u[i].frame_first < 0 || u[i].frame_count < 0 || u[i].out_row < 0)
+      return fail(MMB_E_INVALID, "negative field in unit table");
+  }
+  return MMB_OK;
+}
+
+static void build_prefix(const mmb_plan* p, const mmb_track* u, int32_t n, std::vector<int32_t>& prefix,
+                         int64_t* rows) {
+  prefix.assign(n + 1, 0);
+  int64_t r = 0;
+  for (int32_t i = 0; i < n; ++i) {
+    const int64_t c = (u[i].frame_count + p->chunk_frames - 1) / p->chunk_frames;
+    prefix[i + 1] = prefix[i] + (int32_t)c;
+    r += u[i].frame_count;
+  }
+  *rows = r;
+}
+
+extern "C" int mmb_layout_destroy(mmb_layout* l) {
+  if (!l) return MMB_OK;
+  cudaFree(l->d_tracks); cudaFree(l->d_prefix);
+  delete l;
+  return MMB_OK;
+}
+
+extern "C" int mmb_layout_create(const mmb_plan* p, const mmb_track* units, int32_t n, mmb_layout** out) {
+  if (!p || !out) return fail(MMB_E_INVALID, "null argument");
+  *out = nullptr;
+  int rc = validate_units(units, n);
+  if (rc) return rc;
+  CU(cudaSetDevice(p->cfg.device));
+  mmb_layout* l = new (std::nothrow) mmb_layout();
+  if (!l) return fail(MMB_E_NOMEM, "out of host memory");
+  std::vector<int32_t> prefix;
+  build_prefix(p, units, n, prefix, &l->total_rows);
+  l->n = n;
+  l->total_chunks = prefix[n];
+  std::vector<Track> t(n);
+  std::memcpy(t.data(), units, sizeof(Track) * n);
+  cudaError_t e;
+  if ((e = upload(&l->d_tracks, t)) != cudaSuccess || (e = upload(&l->d_prefix, prefix)) != cudaSuccess) {
+    mmb_layout_destroy(l);
+    return cuda_fail(e, "layout upload");
+  }
+  *out = l;
+  return MMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ run
+static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
+  if (!o) return fail(MMB_E_INVALID, "outputs is null");
+  const bool band_out = o->filt || o->log || o->diff || o->odf;
+  if (!o->stft && !o->spec && !band_out) return fail(MMB_E_INVALID, "no output requested");
+  if (band_out && p->cfg.num_bands == 0)
+    return fail(MMB_E_UNSUPPORTED, "filt/log/diff/odf outputs need a filterbank in the plan");
+  if ((o->diff || o->odf) && p->cfg.diff_frames < 1)
+    return fail(MMB_E_INVALID, "diff/odf outputs need diff_frames >= 1 in the plan");
+  return MMB_OK;
+}
+
+static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_prefix, int32_t n, int32_t chunks,
+                  const void* pcm_dev, const mmb_outputs* o, cudaStream_t stream) {
+  FrontendParams fp;
+  std::memset(&fp, 0, sizeof(fp));
+  fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunk_prefix = d_prefix; fp.n_tracks = n; fp.total_chunks = chunks;
+  fp.chunk_frames = p->chunk_frames; fp.hop = p->cfg.hop_size; fp.origin = p->cfg.origin; fp.span_cap = p->span_cap;
+  fp.win = p->d_win; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
+  const bool band_out = o->filt || o->log || o->diff || o->odf;
+  fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only stft/spec are wanted
+  fp.nnz = band_out ? p->nnz : 0;
+  fp.band_start = p->d_bstart; fp.band_len = p->d_blen; fp.band_woff = p->d_bwoff; fp.weights = p->d_w;
+  fp.mul = p->cfg.mul; fp.add = p->cfg.add; fp.log_mode = p->cfg.log_mode;
+  fp.diff_frames = p->cfg.diff_frames; fp.max_bins = p->cfg.diff_max_bins; fp.positive = p->cfg.positive_diffs;
+  fp.circular_shift = p->cfg.circular_shift;
+  fp.out_stft = (float2*)o->stft; fp.ld_stft = o->ld_stft; fp.out_spec = o->spec; fp.ld_spec = o->ld_spec;
+  fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
+  fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;
+  // the shared-memory layout depends on n_bands/nnz actually used
+  const mmb::SmemLayout L = mmb::smem_layout(p->cfg.frame_size, fp.n_bands, fp.nnz, p->span_cap, p->sample_bytes);
+  int grid = p->ctas_per_sm * p->num_sms;
+  if (grid > chunks) grid = chunks;
+  if (grid < 1) return MMB_OK;
+  cudaError_t e = mmb::launch_frontend(p->cfg.frame_size, p->sample_bytes, fp, grid, L.total, stream);
+  if (e != cudaSuccess) return cuda_fail(e, "frontend kernel launch");
+  return MMB_OK;
+}
+
+extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_dev, const mmb_outputs* outs,
+                       void* stream, int32_t* launches) {
+  if (launches) *launches = 0;
+  if (!p || !l || !pcm_dev) return fail(MMB_E_INVALID, "null argument");
+  int rc = check_outputs(p, outs);
+  if (rc) return rc;
+  CU(cudaSetDevice(p->cfg.device));
+  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, pcm_dev, outs, (cudaStream_t)stream);
+  if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
+  return rc;
+}
+
+extern "C" int mmb_host_alloc(void** ptr, int64_t bytes) {
+  if (!ptr || bytes < 0) return fail(MMB_E_INVALID, "bad argument");
+  CU(cudaHostAlloc(ptr, (size_t)bytes, cudaHostAllocDefault));
+  return MMB_OK;
+}
+extern "C" int mmb_host_free(void* ptr) {
+  if (ptr) CU(cudaFreeHost(ptr));
+  return MMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ host path
+// mmb_run_host: units are cut into groups of <= kGroupBytes of PCM; each group goes through one of
+// kSlots staging slots (own stream: H2D copy -> kernel -> D2H copies), so the copy engines and the SMs
+// work on different groups at the same time.  Requires units ordered by pcm_offset and out_row.
+namespace {
+constexpr int kSlots = 3;
+constexpr int64_t kGroupBytes = 64ll << 20;
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  void* d_pcm = nullptr; size_t pcm_cap = 0;
+  void* d_out[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; size_t out_cap[6] = {0, 0, 0, 0, 0, 0};
+  Track* d_tracks = nullptr; size_t tracks_cap = 0;
+  int32_t* d_prefix = nullptr; size_t prefix_cap = 0;
+};
+
+static cudaError_t ensure(void** p, size_t* cap, size_t need) {
+  if (need <= *cap) return cudaSuccess;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  cudaError_t e = cudaMalloc(p, need);
+  if (e == cudaSuccess) *cap = need;
+  return e;
+}
+}  // namespace
+
+extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n, const void* pcm_host,
+                            const mmb_outputs* oh, int32_t* launches) {
+  if (launches) *launches = 0;
+  if (!p || !pcm_host) return fail(MMB_E_INVALID, "null argument");
+  int rc = validate_units(units, n);
+  if (rc) return rc;
+  rc = check_outputs(p, oh);
+  if (rc) return rc;
+  CU(cudaSetDevice(p->cfg.device));
+  for (int32_t i = 1; i < n; ++i)
+    if (units[i].pcm_offset < units[i - 1].pcm_offset || units[i].out_row < units[i - 1].out_row + units[i - 1].frame_count)
+      return fail(MMB_E_INVALID, "mmb_run_host needs units ordered by pcm_offset with consecutive, non-overlapping out_row ranges");
+  const int K = p->cfg.frame_size / 2, B = p->cfg.num_bands;
+  const size_t sb = (size_t)p->sample_bytes;
+  // widths (elements) and element sizes of the six outputs: stft spec filt log diff odf
+  void* hptr[6] = {oh->stft, oh->spec, oh->filt, oh->log, oh->diff, oh->odf};
+  const int64_t hld[6] = {oh->ld_stft, oh->ld_spec, oh->ld_filt, oh->ld_log, oh->ld_diff, 1};
+  const int width[6] = {K, K, B, B, B, 1};
+  const size_t esz[6] = {8, 4, 4, 4, 4, 4};
+  for (int k = 0; k < 6; ++k)
+    if (hptr[k] && hld[k] < width[k]) return fail(MMB_E_INVALID, "leading dimension smaller than the row width");
+
+  Slot slots[kSlots];
+  int used_slots = 0, n_launch = 0;
+  int status = MMB_OK;
+  auto cleanup = [&]() {
+    for (int s = 0; s < kSlots; ++s) {
+      if (slots[s].stream) { cudaStreamSynchronize(slots[s].stream); cudaStreamDestroy(slots[s].stream); }
+      cudaFree(slots[s].d_pcm); cudaFree(slots[s].d_tracks); cudaFree(slots[s].d_prefix);
+      for (int k = 0; k < 6; ++k) cudaFree(slots[s].d_out[k]);
+    }
+  };
+#define CUS(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { status = cuda_fail(e_, #x); goto done; } } while (0)
+  {
+    std::vector<Track> tab;
+    std::vector<int32_t> prefix;
+    int32_t i0 = 0;
+    int g = 0;
+    while (i0 < n) {
+      // ---- group [i0, i1)
+      int32_t i1 = i0;
+      const int64_t pcm0 = units[i0].pcm_offset;
+      int64_t pcm1 = pcm0;
+      while (i1 < n) {
+        const int64_t e1 = units[i1].pcm_offset + units[i1].pcm_len;
+        const int64_t np1 = e1 > pcm1 ? e1 : pcm1;
+        if (i1 > i0 && (np1 - pcm0) * (int64_t)sb > kGroupBytes) break;
+        pcm1 = np1; ++i1;
+      }
+      const int64_t row0 = units[i0].out_row;
+      const int64_t row1 = units[i1 - 1].out_row + units[i1 - 1].frame_count;
+      const int64_t rows = row1 - row0;
+      Slot& S = slots[g % kSlots];
+      if (!S.stream) { CUS(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking)); ++used_slots; }
+      // the slot's previous group must be fully drained before its buffers are reused
+      CUS(cudaStreamSynchronize(S.stream));
+      tab.assign(i1 - i0, Track());
+      for (int32_t i = i0; i < i1; ++i) {
+        std::memcpy(&tab[i - i0], &units[i], sizeof(Track));
+        tab[i - i0].pcm_offset -= pcm0;
+        tab[i - i0].out_row -= row0;
+      }
+      int64_t dummy;
+      build_prefix(p, reinterpret_cast<const mmb_track*>(tab.data()), i1 - i0, prefix, &dummy);
+      size_t pcm_bytes = (size_t)(pcm1 - pcm0) * sb;
+      if (pcm_bytes == 0) pcm_bytes = sb;
+      CUS(ensure(&S.d_pcm, &S.pcm_cap, pcm_bytes));
+      CUS(ensure((void**)&S.d_tracks, &S.tracks_cap, tab.size() * sizeof(Track)));
+      CUS(ensure((void**)&S.d_prefix, &S.prefix_cap, prefix.size() * sizeof(int32_t)));
+      mmb_outputs od;
+      std::memset(&od, 0, sizeof(od));
+      for (int k = 0; k < 6; ++k) {
+        if (!hptr[k]) continue;
+        CUS(ensure(&S.d_out[k], &S.out_cap[k], (size_t)(rows > 0 ? rows : 1) * width[k] * esz[k]));
+      }
+      od.stft = hptr[0] ? S.d_out[0] : nullptr; od.ld_stft = K;
+      od.spec = hptr[1] ? (float*)S.d_out[1] : nullptr; od.ld_spec = K;
+      od.filt = hptr[2] ? (float*)S.d_out[2] : nullptr; od.ld_filt = B;
+      od.log = hptr[3] ? (float*)S.d_out[3] : nullptr; od.ld_log = B;
+      od.diff = hptr[4] ? (float*)S.d_out[4] : nullptr; od.ld_diff = B;
+      od.odf = hptr[5] ? (float*)S.d_out[5] : nullptr;
+      CUS(cudaMemcpyAsync(S.d_tracks, tab.data(), tab.size() * sizeof(Track), cudaMemcpyHostToDevice, S.stream));
+      CUS(cudaMemcpyAsync(S.d_prefix, prefix.data(), prefix.size() * sizeof(int32_t), cudaMemcpyHostToDevice, S.stream));
+      CUS(cudaMemcpyAsync(S.d_pcm, (const char*)pcm_host + (size_t)pcm0 * sb, (size_t)(pcm1 - pcm0) * sb,
+                          cudaMemcpyHostToDevice, S.stream));
+      // pageable tab/prefix vectors are reused by the next group: the async copies above are staged
+      // synchronously by the runtime for pageable memory, so this is safe.
+      if (prefix.back() > 0) {
+        status = launch(p, S.d_tracks, S.d_prefix, (int32_t)tab.size(), prefix.back(), S.d_pcm, &od, S.stream);
+        if (status) goto done;
+        ++n_launch;
+        for (int k = 0; k < 6; ++k) {
+          if (!hptr[k]) continue;
+          char* dst = (char*)hptr[k] + (size_t)row0 * hld[k] * esz[k];
+          CUS(cudaMemcpy2DAsync(dst, (size_t)hld[k] * esz[k], S.d_out[k], (size_t)width[k] * esz[k],
+                                (size_t)width[k] * esz[k], (size_t)rows, cudaMemcpyDeviceToHost, S.stream));
+        }
+      }
+      i0 = i1; ++g;
+    }
+    for (int s = 0; s < kSlots; ++s)
+      if (slots[s].stream) CUS(cudaStreamSynchronize(slots[s].stream));
+  }
+done:
+#undef CUS
+  cleanup();
+  (void)used_slots;
+  if (launches) *launches = n_launch;
+  return status;
+}

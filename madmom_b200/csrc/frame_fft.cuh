@@ -1,0 +1,140 @@
+// Per-frame-size wrappers around the 1024-point warp FFT core (fft_core.cuh):
+//   N = 2048 : one frame per core call, even/odd packing z[n] = x[2n] + i x[2n+1], split with W2048^k
+//   N = 1024 : two frames per core call, z[n] = xA[n] + i xB[n], twiddle-free split
+//   N = 4096 : one frame per two core calls: radix-2 DIF pre-stage on the packed 2048-point sequence
+//              (y0 = z[n] + z[n+1024], y1 = (z[n] - z[n+1024]) W2048^n), each half split with W4096^k
+// All variants produce X[k] = sum_n x[n] w[n] exp(-2 pi i k n / N), k = 0 .. N/2-1  (Nyquist dropped, as
+// madmom/audio/stft.py:93-95 does by default).  The window passed in is fft_window * 0.5 (exact scaling;
+// it absorbs the 1/2 of the real-FFT split), see capi.cu.
+//
+// Sample type S is int16_t or float (madmom keeps integer PCM un-scaled and scales the window instead,
+// madmom/audio/stft.py:331-349).
+#pragma once
+#include "fft_core.cuh"
+
+namespace mmb {
+
+template <typename S>
+MMB_HD float to_f32(S s) { return (float)s; }
+
+// ------------------------------------------------------------------------------------------ loads
+// x points at the first sample of the frame inside the staged PCM span (any alignment).
+template <typename S>
+MMB_HD void load_frame_2048(int lane, float2 (&v)[32], const S* x, const float* __restrict__ win) {
+#pragma unroll
+  for (int m = 0; m < 32; ++m) {
+    const int n = lane + 32 * m;
+    const float2 w = *reinterpret_cast<const float2*>(win + 2 * n);
+    v[m] = make_float2(to_f32(x[2 * n]) * w.x, to_f32(x[2 * n + 1]) * w.y);
+  }
+}
+
+// two frames (xb may be null -> zero imaginary part)
+template <typename S>
+MMB_HD void load_frames_1024(int lane, float2 (&v)[32], const S* xa, const S* xb, const float* __restrict__ win) {
+#pragma unroll
+  for (int m = 0; m < 32; ++m) {
+    const int n = lane + 32 * m;
+    const float w = win[n];
+    v[m] = make_float2(to_f32(xa[n]) * w, xb ? to_f32(xb[n]) * w : 0.0f);
+  }
+}
+
+// half c (0 or 1) of a 4096-point frame; tw2k[q*32 + lane] = W2048^(lane + 32 q)
+template <typename S>
+MMB_HD void load_frame_4096(int lane, int c, float2 (&v)[32], const S* x, const float* __restrict__ win,
+                            const float2* __restrict__ tw2k) {
+#pragma unroll
+  for (int m = 0; m < 32; ++m) {
+    const int n = lane + 32 * m;
+    const float2 w0 = *reinterpret_cast<const float2*>(win + 2 * n);
+    const float2 w1 = *reinterpret_cast<const float2*>(win + 2 * n + 2048);
+    const float2 z0 = make_float2(to_f32(x[2 * n]) * w0.x, to_f32(x[2 * n + 1]) * w0.y);
+    const float2 z1 = make_float2(to_f32(x[2 * n + 2048]) * w1.x, to_f32(x[2 * n + 2049]) * w1.y);
+    if (c == 0) {
+      v[m] = make_float2(z0.x + z1.x, z0.y + z1.y);
+    } else {
+      v[m] = cmul(make_float2(z0.x - z1.x, z0.y - z1.y), tw2k[m * 32 + lane]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ splits
+// Output sink: magnitudes into warp scratch `mag` (always), and optionally complex bins / magnitudes
+// straight to global memory (row pointers, may be null).  `sgn_odd` = -1 when circular_shift is set:
+// swapping the two halves of the frame multiplies X[k] by (-1)^k (madmom/audio/stft.py:106-119).
+struct BinSink {
+  float* mag;        // warp scratch, K floats
+  float2* stft_row;  // global, K complex, or null
+  float* spec_row;   // global, K floats, or null
+  float sgn_odd;     // +1 or -1
+  MMB_HD void put(int k, float re, float im) const {
+    const float m = mag_of(re, im);
+    mag[k] = m;
+    if (spec_row) spec_row[k] = m;
+    if (stft_row) {
+      const float s = (k & 1) ? sgn_odd : 1.0f;
+      stft_row[k] = make_float2(re * s, im * s);
+    }
+  }
+};
+
+// N = 2048.  v[r] = Z[lane + 32 brev5(r)], zs[k] valid for k in [512, 1024]  (zs[1024] = Z[0]).
+MMB_HD void split_2048(int lane, const float2 (&v)[32], const float2* zs, const float2* __restrict__ tw2k,
+                       const BinSink& out) {
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    const float2 zk = v[brev5(q)];
+    const int k = lane + 32 * q, kp = 1024 - k;
+    const float2 zp = zs[kp];
+    const float2 w = tw2k[q * 32 + lane];
+    const float ar = zk.x + zp.x, ai = zk.y - zp.y;
+    const float br = zk.x - zp.x, bi = zk.y + zp.y;
+    const float tr = w.x * br - w.y * bi, ti = w.x * bi + w.y * br;
+    out.put(k, ar + ti, ai - tr);
+    if (kp < 1024) out.put(kp, ar - ti, -(ai + tr));
+  }
+  if (lane == 0) {                       // k = 512 pairs with itself: X[512] = conj(Z[512])
+    const float2 z = v[brev5(16)];
+    out.put(512, 2.0f * z.x, -2.0f * z.y);
+  }
+}
+
+// N = 1024, two frames.  Bins of frame A via outA, frame B via outB (k in [0, 512)).
+MMB_HD void split_1024x2(int lane, const float2 (&v)[32], const float2* zs, const BinSink& outA,
+                         const BinSink& outB, bool haveB) {
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    const float2 zk = v[brev5(q)];
+    const int k = lane + 32 * q;
+    const float2 zp = zs[1024 - k];
+    outA.put(k, zk.x + zp.x, zk.y - zp.y);              // (Z[k] + conj Z[-k]) / 2
+    if (haveB) outB.put(k, zk.y + zp.y, zp.x - zk.x);   // (Z[k] - conj Z[-k]) / 2i
+  }
+}
+
+// N = 4096, half c.  Even bins (c = 0) pair as (j, 1024 - j) with twiddle W4096^(2j) = W2048^j;
+// odd bins (c = 1) pair as (j, 1023 - j) with twiddle W4096^(2j+1) = tw4k[q*32 + lane].
+MMB_HD void split_4096(int lane, int c, const float2 (&v)[32], const float2* zs,
+                       const float2* __restrict__ tw2k, const float2* __restrict__ tw4k, const BinSink& out) {
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    const float2 zk = v[brev5(q)];
+    const int j = lane + 32 * q;
+    const int jp = (c == 0) ? 1024 - j : 1023 - j;
+    const float2 zp = zs[jp];
+    const float2 w = (c == 0) ? tw2k[q * 32 + lane] : tw4k[q * 32 + lane];
+    const float ar = zk.x + zp.x, ai = zk.y - zp.y;
+    const float br = zk.x - zp.x, bi = zk.y + zp.y;
+    const float tr = w.x * br - w.y * bi, ti = w.x * bi + w.y * br;
+    const int k = 2 * j + c, kp = 2 * jp + c;
+    out.put(k, ar + ti, ai - tr);
+    if (kp < 2048) out.put(kp, ar - ti, -(ai + tr));
+  }
+  if (c == 0 && lane == 0) {             // bin 1024 pairs with itself
+    const float2 z = v[brev5(16)];
+    out.put(1024, 2.0f * z.x, -2.0f * z.y);
+  }
+}
+
+}  // namespace mmb

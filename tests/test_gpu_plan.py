@@ -1,0 +1,210 @@
+"""GPU parity tests of the C-ABI path (libmadmom_b200.so through madmom_b200._lib.FrontEndPlan) against the
+CPU oracle on the same inputs.  Bounds: integer outputs bit-exact; float32 features
+|gpu - ref| <= 1e-5 + 1e-4 |ref|."""
+import numpy as np
+import pytest
+
+from conftest import assert_close
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+def _plan_for(x_dtype, N, hop, bpo, norm, mul=1.0, add=1.0, ratio=0.5, max_bins=None, positive=True, circ=False,
+              origin=0, chunk_frames=0):
+    from oracle import frontend as O
+    from madmom_b200 import _lib
+    win = np.hanning(N)
+    fw = O.fft_window(win, N, x_dtype)
+    fb = O.logarithmic_filterbank(O.fft_frequencies(N // 2, 44100), bpo, 30., 17000., 440., norm, True)
+    d = O.diff_frames(ratio, hop, N, win)
+    plan = _lib.FrontEndPlan(N, hop, fw, pcm_dtype=x_dtype, origin=origin, circular_shift=circ, filterbank=fb,
+                             log_mode=_lib.LOG_LOG10, mul=mul, add=add, diff_frames=d, diff_max_bins=max_bins or 0,
+                             positive_diffs=positive, chunk_frames=chunk_frames)
+    recipe = dict(frame_size=N, hop_size=hop, origin=origin, num_bands=bpo, norm_filters=norm, mul=mul, add=add,
+                  diff_ratio=ratio, diff_max_bins=max_bins, positive_diffs=positive, circular_shift=circ)
+    return plan, recipe
+
+
+def _run_all(plan, tracks, hop):
+    """tracks: list of 1-D numpy arrays.  Returns dict of numpy outputs for the concatenated batch."""
+    from madmom_b200 import _lib
+    lens = [len(t) for t in tracks]
+    T = [_lib.num_frames(n, hop) for n in lens]
+    units = _lib.make_units(lens, T)
+    pcm = torch.from_numpy(np.concatenate(tracks)).cuda()
+    rows, K, B = int(sum(T)), plan.num_bins, plan.num_bands
+    outs = {"stft": torch.full((rows, K), float("nan"), dtype=torch.complex64, device="cuda"),
+            "spec": torch.full((rows, K), float("nan"), device="cuda"),
+            "filt": torch.full((rows, B), float("nan"), device="cuda"),
+            "log": torch.full((rows, B), float("nan"), device="cuda"),
+            "diff": torch.full((rows, B), float("nan"), device="cuda"),
+            "odf": torch.full((rows,), float("nan"), device="cuda")}
+    plan.run(pcm, units, outs)
+    torch.cuda.synchronize()
+    return {k: v.cpu().numpy() for k, v in outs.items()}, T
+
+
+def _check_stages(got, ref, what):
+    scale = np.abs(ref["stft"]).max()
+    # complex STFT: the reference rounds a float64 FFT to complex64; an FP32 FFT differs by ~1e-7 * max|X|
+    assert np.abs(got["stft"] - ref["stft"]).max() <= 2e-6 * scale, what
+    assert np.abs(got["spec"] - ref["spec"]).max() <= 2e-6 * scale, what
+    assert_close(got["filt"], ref["filt"], what=what + " filt")
+    assert_close(got["log"], ref["log"], what=what + " log")
+    assert_close(got["diff"], ref["diff"], what=what + " diff")
+    assert_close(got["odf"], ref["odf"], what=what + " odf")
+
+
+@pytest.mark.parametrize("N", [2048, 1024, 4096])
+def test_sample_wav_all_stages(sample_pcm, N):
+    from oracle import frontend as O
+    plan, recipe = _plan_for(np.int16, N, 441., 24, False, max_bins=3)
+    got, T = _run_all(plan, [sample_pcm], 441.)
+    assert T == [281]
+    ref = O.run_recipe(sample_pcm, recipe, stages=True)
+    _check_stages(got, ref, "sample.wav N=%d" % N)
+    assert not got["diff"][:ref["diff_frames"]].any()
+
+
+def test_superflux_golden(sample_pcm, ref_sample):
+    """Config 1 against the vectors produced by the real reference (tests/golden/make_golden.py) and the
+    reference's own literals (tests/test_audio_spectrogram.py:584-591)."""
+    plan, _ = _plan_for(np.int16, 2048, 441., 24, False, max_bins=3)
+    got, _ = _run_all(plan, [sample_pcm], 441.)
+    assert_close(got["diff"], ref_sample["superflux_diff"], what="superflux vs reference")
+    assert_close(got["log"], ref_sample["logfilt24"], what="logfilt24 vs reference")
+    assert_close(got["odf"], ref_sample["odf_superflux_100"], what="odf vs reference")
+    assert np.allclose(got["diff"][1, :8], [0.11168772, 0.12317812, 0, 0, 0.03797626, 0.18899226, 0, 0.0903399],
+                       atol=1e-5)
+    assert np.allclose(got["spec"][0, :8], [3.15249, 4.00272, 5.66156, 6.30141, 6.02199, 10.84909, 17.83130,
+                                            19.44511])
+    rows = ref_sample["rows"]
+    scale = np.abs(ref_sample["stft_rows"]).max()
+    assert np.abs(got["stft"][rows] - ref_sample["stft_rows"]).max() <= 2e-6 * scale
+
+
+def test_fps200_fractional_hop_and_peaks(sample_pcm, ref_sample):
+    """bin/SuperFlux recipe: hop 220.5 (frame starts int(i*220.5) must be exact), d=2; onset indices from the
+    GPU ODF must equal the reference's, bit-exact."""
+    from oracle import frontend as O
+    hop = 44100 / 200.
+    plan, recipe = _plan_for(np.int16, 2048, hop, 24, False, max_bins=3)
+    got, T = _run_all(plan, [sample_pcm], hop)
+    assert T == [561] and plan.diff_frames == 2
+    assert_close(got["odf"], ref_sample["odf_superflux_200"], what="superflux fps200")
+    assert np.allclose(got["odf"], ref_sample["fixture_act_super_flux"], atol=1e-5)   # tests/test_bin.py:956-1003
+    peaks = O.peak_picking(got["odf"], 1.1, None, 30, 0, 2, 10)
+    assert np.array_equal(peaks, ref_sample["peaks_superflux_200"])
+    on = O.onset_peak_picking(got["odf"], 200, threshold=1.1, pre_max=0.01, post_max=0.05, pre_avg=0.15,
+                              combine=0.03)
+    assert np.array_equal(on, ref_sample["onsets_superflux_200"])
+
+
+def test_circular_shift_stft(sample_pcm, ref_sample):
+    plan, _ = _plan_for(np.int16, 2048, 441., 24, False, circ=True)
+    got, _ = _run_all(plan, [sample_pcm], 441.)
+    rows = ref_sample["rows"]
+    scale = np.abs(ref_sample["stft_circ_rows"]).max()
+    assert np.abs(got["stft"][rows] - ref_sample["stft_circ_rows"]).max() <= 2e-6 * scale
+
+
+@pytest.mark.parametrize("N,bpo,norm,mul,ratio", [(2048, 12, False, 1., .5), (1024, 6, True, 5., .25),
+                                                   (4096, 6, True, 5., .25), (4096, 6, True, 1., .5)])
+def test_ragged_batch_vs_oracle(N, bpo, norm, mul, ratio):
+    """Batch of ragged synthetic tracks (incl. shorter than one frame / one hop) in one launch; small chunks
+    so that chunk boundaries, lead-in recomputation and track edges are all exercised."""
+    from oracle import frontend as O
+    from madmom_b200.synth import make_track
+    lens = [44100, 1, 440, 441, 442, 30011, 2048, 5000, 77777]
+    tracks = [make_track(1000 + i, num_samples=n) for i, n in enumerate(lens)]
+    plan, recipe = _plan_for(np.int16, N, 441., bpo, norm, mul=mul, ratio=ratio, chunk_frames=13)
+    got, T = _run_all(plan, tracks, 441.)
+    r0 = 0
+    for x, t in zip(tracks, T):
+        ref = O.run_recipe(x, recipe, stages=True)
+        sl = {k: v[r0:r0 + t] for k, v in got.items()}
+        _check_stages(sl, ref, "track len %d N=%d" % (len(x), N))
+        r0 += t
+
+
+def test_float32_pcm(ref_synth):
+    from oracle import frontend as O
+    from madmom_b200.synth import make_track
+    x = make_track(1000, 3.0, dtype=np.float32)
+    plan, recipe = _plan_for(np.float32, 2048, 441., 24, False, max_bins=3)
+    got, _ = _run_all(plan, [x], 441.)
+    assert_close(got["diff"], ref_synth["s1000_f32_superflux"], what="float32 pcm superflux")
+
+
+def test_signed_diff_and_origin():
+    from oracle import frontend as O
+    from madmom_b200.synth import make_track
+    x = make_track(5, 2.0)
+    for origin in ("online", "stream", 100):
+        o = O.resolve_origin(origin, 2048)
+        plan, recipe = _plan_for(np.int16, 2048, 441., 12, True, positive=False, max_bins=3, origin=o)
+        got, _ = _run_all(plan, [x], 441.)
+        ref = O.run_recipe(x, recipe, stages=True)
+        _check_stages(got, ref, "origin %s" % origin)
+
+
+def test_frame_range_units_match_whole_signal():
+    """Shard mode: frame ranges with a PCM halo reproduce the unsharded rows bit for bit."""
+    from madmom_b200 import _lib
+    from madmom_b200.synth import make_track
+    x = make_track(9, 6.0)
+    hop, N = 441., 2048
+    plan, _ = _plan_for(np.int16, N, hop, 24, False, max_bins=3)
+    whole, T = _run_all(plan, [x], hop)
+    T = T[0]
+    d = plan.diff_frames
+    cuts = [0, 100, 333, T]
+    units = np.zeros(3, dtype=_lib.TRACK_DTYPE)
+    pieces, off = [], 0
+    for i in range(3):
+        f0, f1 = cuts[i], cuts[i + 1]
+        s0 = max(_lib.frame_start(max(f0 - d, 0), N, hop, 0), 0)
+        s1 = min(_lib.frame_start(f1 - 1, N, hop, 0) + N, len(x))
+        pieces.append(x[s0:s1])
+        units[i] = (off, s1 - s0, s0, f0, f1 - f0, f0)
+        off += s1 - s0
+    pcm = torch.from_numpy(np.concatenate(pieces)).cuda()
+    outs = {"diff": torch.zeros((T, plan.num_bands), device="cuda"), "odf": torch.zeros((T,), device="cuda")}
+    plan.run(pcm, units, outs)
+    torch.cuda.synchronize()
+    assert np.array_equal(outs["diff"].cpu().numpy(), whole["diff"])
+    assert np.array_equal(outs["odf"].cpu().numpy(), whole["odf"])
+
+
+def test_host_path_equals_device_path():
+    from madmom_b200 import _lib
+    from madmom_b200.synth import make_track
+    tracks = [make_track(50 + i, num_samples=n) for i, n in enumerate([40000, 12345, 88200])]
+    plan, _ = _plan_for(np.int16, 2048, 441., 12, False)
+    dev, T = _run_all(plan, tracks, 441.)
+    units = _lib.make_units([len(t) for t in tracks], T)
+    rows = sum(T)
+    pcm = np.concatenate(tracks)
+    stacked = np.zeros((rows, 2 * plan.num_bands), np.float32)       # hstack((log, diff)) written in place
+    odf = np.zeros(rows, np.float32)
+    n = plan.run_host(pcm, units, {"log": stacked[:, :plan.num_bands], "diff": stacked[:, plan.num_bands:],
+                                   "odf": odf})
+    assert n >= 1
+    assert np.array_equal(stacked[:, :plan.num_bands], dev["log"])
+    assert np.array_equal(stacked[:, plan.num_bands:], dev["diff"])
+    assert np.array_equal(odf, dev["odf"])
+
+
+def test_errors():
+    from madmom_b200 import _lib
+    with pytest.raises(NotImplementedError):
+        _lib.FrontEndPlan(512, 441., np.hanning(512))
+    plan = _lib.FrontEndPlan(2048, 441., np.hanning(2048) / 32767.)
+    pcm = torch.zeros(10000, dtype=torch.int16, device="cuda")
+    units = _lib.make_units([10000], [23])
+    with pytest.raises(NotImplementedError):
+        plan.run(pcm, units, {"log": torch.zeros((23, 0), device="cuda")})
+    with pytest.raises(ValueError):
+        plan.run(pcm, units, {})

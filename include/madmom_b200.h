@@ -44,7 +44,7 @@ enum {
 };
 
 enum { MMB_PCM_I16 = 0, MMB_PCM_F32 = 1 };
-enum { MMB_LOG_NONE = 0, MMB_LOG_LOG10 = 1, MMB_LOG_MULADD = 2 };
+enum { MMB_LOG_NONE = 0, MMB_LOG_LOG10 = 1, MMB_LOG_MULADD = 2, MMB_LOG_LN = 3, MMB_LOG_LOG2 = 4 };
 
 typedef struct mmb_plan mmb_plan;     /* immutable after creation, usable from any host thread */
 typedef struct mmb_layout mmb_layout; /* device-resident description of a batch of units         */
@@ -63,7 +63,7 @@ typedef struct mmb_config {
   const int32_t* band_start; /* [num_bands] first non-zero bin                                             */
   const int32_t* band_len;   /* [num_bands] run length                                                     */
   const float* band_weights; /* concatenated runs                                                          */
-  int32_t log_mode;        /* MMB_LOG_*: none / log10(x*mul+add) / x*mul+add                               */
+  int32_t log_mode;        /* MMB_LOG_*: none / log10(x*mul+add) / x*mul+add / ln(..) / log2(..)            */
   float mul, add;
   int32_t diff_frames;     /* d >= 1 (from _diff_frames, spectrogram.py:834-864), 0: no difference stage   */
   int32_t diff_max_bins;   /* frequency maximum-filter width (<= 1: none), scipy 'reflect' borders         */

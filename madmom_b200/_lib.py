@@ -11,7 +11,7 @@ LIBPATH = os.path.join(_HERE, "lib", "libmadmom_b200.so")
 
 MMB_OK, MMB_E_INVALID, MMB_E_UNSUPPORTED, MMB_E_CUDA, MMB_E_NOMEM = 0, -1, -2, -3, -4
 PCM_I16, PCM_F32 = 0, 1
-LOG_NONE, LOG_LOG10, LOG_MULADD = 0, 1, 2
+LOG_NONE, LOG_LOG10, LOG_MULADD, LOG_LN, LOG_LOG2 = 0, 1, 2, 3, 4
 
 c_i32, c_i64, c_f32, c_f64, c_vp = ctypes.c_int32, ctypes.c_int64, ctypes.c_float, ctypes.c_double, ctypes.c_void_p
 

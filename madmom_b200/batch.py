@@ -1,0 +1,143 @@
+"""Batched front end: many tracks (or frame ranges of one long signal) through the fused kernel in one launch
+per recipe.  This is the data-parallel entry point behind the processor classes; the reference's equivalent
+is one Python process per file (`process_batch`, madmom/processors.py:637-713).
+
+    fe = BatchFrontEnd(recipe.LOGFILTSPECFLUX)                  # one plan on the current CUDA device
+    out = fe.run_device(pcm_cuda, lengths, ("diff", "odf"))     # tensors stay on the GPU
+    out = fe.run_host(pcm_pinned, lengths, ("diff", "odf"))     # host in, host out (H2D/kernel/D2H overlapped)
+
+Several recipes (the multi-resolution stack of RNNOnsetProcessor / RNNBeatProcessor) write directly into the
+column blocks of one `(rows, sum 2 B_i)` matrix, which is the reference's np.hstack of hstack((spec, diff)).
+"""
+import numpy as np
+
+from . import _lib
+from . import recipe as R
+
+
+def _log_mode(rec):
+    if rec.log is None:
+        return _lib.LOG_MULADD if (rec.mul is not None or rec.add is not None) else _lib.LOG_NONE
+    if rec.log is np.log10:
+        return _lib.LOG_LOG10
+    if rec.log is np.log:
+        return _lib.LOG_LN
+    if rec.log is np.log2:
+        return _lib.LOG_LOG2
+    raise NotImplementedError("log function %r is not available on the GPU path (np.log10, np.log, np.log2 "
+                              "or None)" % (rec.log,))
+
+
+def plan_for(rec, pcm_dtype=np.int16, device=0, chunk_frames=0):
+    """FrontEndPlan of one Recipe."""
+    fb = rec.build_filterbank()
+    d = rec.resolved_diff_frames()
+    return _lib.FrontEndPlan(rec.frame_size, rec.hop_size, R.fft_window(rec.window, rec.frame_size, pcm_dtype),
+                             pcm_dtype=pcm_dtype, origin=R.resolve_origin(rec.origin, rec.frame_size),
+                             circular_shift=rec.circular_shift, filterbank=fb, log_mode=_log_mode(rec),
+                             mul=1.0 if rec.mul is None else rec.mul, add=0.0 if rec.add is None else rec.add,
+                             diff_frames=d, diff_max_bins=rec.diff_max_bins or 0,
+                             positive_diffs=rec.positive_diffs, chunk_frames=chunk_frames, device=device)
+
+
+class BatchFrontEnd(object):
+    def __init__(self, recipes, pcm_dtype=np.int16, device=None, chunk_frames=0):
+        import torch
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = int(device)
+        self.recipes = list(recipes) if isinstance(recipes, (list, tuple)) else [recipes]
+        hops = {r.hop_size for r in self.recipes}
+        ends = {r.end for r in self.recipes}
+        if len(hops) != 1 or len(ends) != 1:
+            raise ValueError("all recipes of a stack must share hop_size and end (frame counts must align)")
+        self.hop_size, self.end = hops.pop(), ends.pop()
+        self.pcm_dtype = np.dtype(pcm_dtype)
+        self.plans = [plan_for(r, self.pcm_dtype, self.device, chunk_frames) for r in self.recipes]
+        self.num_bands = [p.num_bands for p in self.plans]
+        self.stack_width = 2 * sum(self.num_bands)
+
+    # ------------------------------------------------------------------------------------------ layout
+    def frame_counts(self, lengths):
+        return [R.num_frames(int(n), self.hop_size, self.end) for n in lengths]
+
+    def units(self, lengths):
+        T = self.frame_counts(lengths)
+        return _lib.make_units(lengths, T), T
+
+    def width(self, name):
+        if name == "stack":
+            return self.stack_width
+        return self.plans[0].width(name)
+
+    def _alloc(self, names, rows, make):
+        out = {}
+        for n in names:
+            if n == "stack":
+                out[n] = make((rows, self.stack_width), "f")
+            elif n == "odf":
+                out[n] = make((rows,), "f")
+            elif n == "stft":
+                out[n] = make((rows, self.width(n)), "c")
+            else:
+                if len(self.plans) != 1:
+                    raise ValueError("output %r needs a single recipe; a stack of recipes produces 'stack'" % n)
+                out[n] = make((rows, self.width(n)), "f")
+        return out
+
+    def _per_plan_outputs(self, out):
+        """[{name: tensor-or-column-view}] per plan."""
+        per = [dict() for _ in self.plans]
+        for n, t in out.items():
+            if n == "stack":
+                c = 0
+                for i, b in enumerate(self.num_bands):
+                    per[i]["log"] = t[:, c:c + b]
+                    per[i]["diff"] = t[:, c + b:c + 2 * b]
+                    c += 2 * b
+            else:
+                per[0][n] = t
+        return per
+
+    # ------------------------------------------------------------------------------------------ device
+    def run_device(self, pcm, lengths=None, outputs=("diff",), out=None, units=None, rows=None):
+        """pcm: 1-D (tracks back to back) or 2-D (equal-length tracks) CUDA tensor.  Returns {name: tensor};
+        row r of every output is frame r of the concatenated batch.  Asynchronous on the current stream."""
+        import torch
+        if pcm.dim() == 2 and lengths is None:
+            lengths = [pcm.shape[1]] * pcm.shape[0]
+        pcm = pcm.reshape(-1)
+        if units is None:
+            units, T = self.units(lengths)
+            rows = int(sum(T))
+        if out is None:
+            def make(shape, kind):
+                return torch.empty(shape, dtype=torch.complex64 if kind == "c" else torch.float32,
+                                   device="cuda:%d" % self.device)
+            out = self._alloc(outputs, rows, make)
+        for plan, o in zip(self.plans, self._per_plan_outputs(out)):
+            if o:
+                plan.run(pcm, units, o)
+        return out
+
+    # ------------------------------------------------------------------------------------------ host
+    def run_host(self, pcm, lengths=None, outputs=("diff",), out=None):
+        """pcm: host array / CPU tensor (pinned for full speed).  Outputs are host tensors (pinned when
+        allocated here).  Returns when they are complete."""
+        import torch
+        if isinstance(pcm, np.ndarray):
+            pcm = torch.from_numpy(pcm)
+        if pcm.dim() == 2 and lengths is None:
+            lengths = [pcm.shape[1]] * pcm.shape[0]
+        pcm = pcm.reshape(-1)
+        units, T = self.units(lengths)
+        rows = int(sum(T))
+        if out is None:
+            def make(shape, kind):
+                return torch.empty(shape, dtype=torch.complex64 if kind == "c" else torch.float32,
+                                   pin_memory=True)
+            out = self._alloc(outputs, rows, make)
+        for plan, o in zip(self.plans, self._per_plan_outputs(out)):
+            if o:
+                plan.run_host(pcm, units, o)
+        return out

@@ -92,7 +92,7 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
     return fail(MMB_E_INVALID, "filterbank arrays are null");
   if (cfg->diff_frames < 0 || cfg->diff_frames > mmb::kMaxDiffFrames)
     return fail(MMB_E_UNSUPPORTED, "diff_frames must be in [0, 16]");
-  if (cfg->log_mode < 0 || cfg->log_mode > 2) return fail(MMB_E_INVALID, "bad log_mode");
+  if (cfg->log_mode < 0 || cfg->log_mode > MMB_LOG_LOG2) return fail(MMB_E_INVALID, "bad log_mode");
   const int K = N / 2;
   std::vector<int32_t> woff(cfg->num_bands);
   int nnz = 0;

@@ -178,6 +178,8 @@ __global__ void __launch_bounds__(kThreads, (N == 4096 ? 1 : 2)) frontend_kernel
         if (p.log_mode != 0) {
           y = __fadd_rn(__fmul_rn(acc, p.mul), p.add);
           if (p.log_mode == 1) y = fast_log10(y);
+          else if (p.log_mode == 3) y = __log2f(y) * 0.69314718055994530942f;
+          else if (p.log_mode == 4) y = __log2f(y);
         }
         s_ring[(int)(g & (kRing - 1)) * nb + b] = y;
       }

@@ -38,7 +38,7 @@ struct FrontendParams {
   const int32_t* band_woff;
   const float* weights;
   float mul, add;
-  int32_t log_mode;              // 0 none, 1 log10
+  int32_t log_mode;              // 0 none, 1 log10, 2 mul/add only, 3 ln, 4 log2
   int32_t diff_frames;           // d >= 1 when a difference is requested
   int32_t max_bins;              // frequency max-filter width (<=1: none)
   int32_t positive;

@@ -248,6 +248,8 @@ class FrontEndPlan(object):
         for name, t in outputs.items():
             if name not in OUTPUT_NAMES:
                 raise ValueError("unknown output %r" % name)
+            if self.num_bands == 0 and name in ("filt", "log", "diff", "odf"):
+                raise NotImplementedError("output %r needs a filterbank in the plan" % name)
             if t.dtype != (torch.complex64 if name == "stft" else torch.float32) or not t.is_cuda:
                 raise ValueError("output %s has the wrong dtype/device" % name)
             if name == "odf":

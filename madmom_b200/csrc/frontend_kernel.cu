@@ -27,7 +27,9 @@ __device__ __forceinline__ long long frame_start_sample(long long g, double hop,
 __device__ __forceinline__ float fast_log10(float y) { return __log2f(y) * 0.30102999566398119521f; }
 
 template <int N, typename S>
-__global__ void __launch_bounds__(kThreads, (N == 4096 ? 1 : 2)) frontend_kernel(const FrontendParams p) {
+__global__ void __launch_bounds__(warps_per_cta(N) * 32, 1) frontend_kernel(const FrontendParams p) {
+  constexpr int kWarps = warps_per_cta(N);
+  constexpr int kThreads = kWarps * 32;
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int FPR = frames_per_round(N);
   constexpr int K = N / 2;
@@ -236,7 +238,7 @@ template <int N, typename S>
 static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
   cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
   if (e != cudaSuccess) return e;
-  frontend_kernel<N, S><<<grid, kThreads, smem_bytes, stream>>>(p);
+  frontend_kernel<N, S><<<grid, warps_per_cta(N) * 32, smem_bytes, stream>>>(p);
   return cudaGetLastError();
 }
 
@@ -258,7 +260,7 @@ template <int N, typename S>
 static cudaError_t occ_one(int smem_bytes, int* out) {
   cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
   if (e != cudaSuccess) return e;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, frontend_kernel<N, S>, kThreads, smem_bytes);
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, frontend_kernel<N, S>, warps_per_cta(N) * 32, smem_bytes);
 }
 
 cudaError_t frontend_max_ctas_per_sm(int N, int sample_bytes, int smem_bytes, int* out) {

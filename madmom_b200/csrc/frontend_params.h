@@ -52,13 +52,13 @@ struct FrontendParams {
   float* out_odf;
 };
 
-constexpr int kWarps = 8;          // warps per CTA
-constexpr int kThreads = kWarps * 32;
+// warps per CTA: one CTA per SM; 16 warps (4 per scheduler) where the per-warp scratch allows it
+__host__ __device__ constexpr int warps_per_cta(int N) { return N == 2048 ? 16 : 8; }
 constexpr int kRing = 32;          // rows of the log-spectrogram ring (>= frames per round + max diff_frames)
 constexpr int kMaxDiffFrames = 16;
 
 // frames one CTA round produces
-__host__ __device__ constexpr int frames_per_round(int N) { return N == 1024 ? 2 * kWarps : kWarps; }
+__host__ __device__ constexpr int frames_per_round(int N) { return N == 1024 ? 2 * warps_per_cta(N) : warps_per_cta(N); }
 // per-warp scratch (bytes): exchange tile (+ magnitudes aliased in its lower 4 KB; separate 8 KB for 4096)
 __host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? 8448 + 8192 : 8448) + 16; }
 
@@ -78,7 +78,7 @@ __host__ __device__ inline SmemLayout smem_layout(int N, int n_bands, int nnz, i
   L.fb_meta = o; o += mmb_align16(n_bands * 3 * 4);
   L.fb_w = o;    o += mmb_align16(nnz * 4);
   L.ring = o;    o += mmb_align16(n_bands > 0 ? kRing * n_bands * 4 : 0);
-  L.scratch = o; o += kWarps * warp_scratch_bytes(N);
+  L.scratch = o; o += warps_per_cta(N) * warp_scratch_bytes(N);
   L.pcm = o;     o += mmb_align16(span_cap * sample_bytes);
   L.total = o;
   return L;

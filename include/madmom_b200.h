@@ -133,6 +133,24 @@ MMB_API int mmb_run_host(const mmb_plan* plan, const mmb_track* units, int32_t n
 MMB_API int mmb_host_alloc(void** ptr, int64_t bytes);
 MMB_API int mmb_host_free(void* ptr);
 
+/* SpectrogramDifference of a (rows, cols) float32 matrix already on the device (unfiltered spectrograms):
+ * out[r, c] = in[r, c] - max_{|j| <= max_bins/2} in[r - d, reflect(c + j)], rows whose lagged row lies before the
+ * start of their signal are zero; rows_per_signal > 0: the matrix holds equal-length signals back to back.
+ * out_dev and odf_dev (row sums) are optional.  Replaces madmom/audio/spectrogram.py:976-993 and the row sum of
+ * madmom/features/onsets.py:163-240. */
+MMB_API int mmb_matrix_diff(const float* in_dev, int64_t ld_in, float* out_dev, int64_t ld_out, float* odf_dev,
+                            int64_t rows, int32_t cols, int64_t rows_per_signal, int32_t diff_frames,
+                            int32_t diff_max_bins, int32_t positive_diffs, void* stream);
+
+/* peak_picking() of madmom/features/onsets.py:875-963 on n_segments activation functions stored back to back in
+ * act_dev (segment s = [seg_offsets[s], seg_offsets[s+1]); seg_offsets_dev may be null for one segment).  All
+ * lengths are in frames.  smooth > 1: Hamming kernel of that length in smooth_kernel_dev (float64).  On return
+ * (stream order) peaks_dev[seg_offsets[s] + j], j < counts_dev[s], holds the ascending local frame indices. */
+MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg_offsets_dev, int32_t n_segments, int64_t n,
+                             double threshold, int32_t smooth, const double* smooth_kernel_dev, int32_t pre_avg,
+                             int32_t post_avg, int32_t pre_max, int32_t post_max, int32_t* peaks_dev,
+                             int32_t* counts_dev, void* stream);
+
 /* Calibration: measured FP32 FMA throughput of `device` in TFLOP/s (dependent FFMA chains on every SM,
  * best of 5, CUDA events).  The front end is FP32-pipe bound; bench.py reports its roofline against this. */
 MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops);

@@ -60,6 +60,9 @@ EXPORTS = {
     "mmb_host_alloc": (c_i32, [ctypes.POINTER(c_vp), c_i64]),
     "mmb_host_free": (c_i32, [c_vp]),
     "mmb_measure_fp32_peak": (c_i32, [c_i32, ctypes.POINTER(c_f64)]),
+    "mmb_matrix_diff": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i32, c_i64, c_i32, c_i32, c_i32, c_vp]),
+    "mmb_peak_picking": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp,
+                                 c_vp, c_vp]),
 }
 
 _lib = None
@@ -289,3 +292,52 @@ class FrontEndPlan(object):
                                       ctypes.byref(o), ctypes.byref(n)))
         launch_count += n.value
         return n.value
+
+
+def _stream(device):
+    import torch
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def matrix_diff(matrix, diff_frames, diff_max_bins=0, positive_diffs=False, rows_per_signal=0, want_diff=True,
+                want_odf=False):
+    """mmb_matrix_diff on a (rows, cols) float32 CUDA tensor.  Returns (diff or None, odf or None)."""
+    global launch_count
+    import torch
+    if not matrix.is_cuda or matrix.dtype != torch.float32 or matrix.dim() != 2 or matrix.stride(1) != 1:
+        raise ValueError("matrix must be a 2-D float32 CUDA tensor with unit column stride")
+    rows, cols = matrix.shape
+    diff = torch.empty((rows, cols), dtype=torch.float32, device=matrix.device) if want_diff else None
+    odf = torch.empty((rows,), dtype=torch.float32, device=matrix.device) if want_odf else None
+    rc = load().mmb_matrix_diff(matrix.data_ptr(), matrix.stride(0), diff.data_ptr() if want_diff else None,
+                                cols, odf.data_ptr() if want_odf else None, rows, cols, int(rows_per_signal),
+                                int(diff_frames), int(diff_max_bins or 0), int(bool(positive_diffs)),
+                                _stream(matrix.device.index))
+    if rc != MMB_OK:
+        raise ValueError("mmb_matrix_diff: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_matrix_diff failed")
+    launch_count += 1 if rows else 0
+    return diff, odf
+
+
+def peak_picking(act, threshold, smooth=0, pre_avg=0, post_avg=0, pre_max=1, post_max=1, seg_offsets=None):
+    """mmb_peak_picking.  act: 1-D float32 CUDA tensor; seg_offsets: None or int64 CUDA tensor [n_seg + 1].
+    Returns (peaks int32 tensor [n], counts int32 tensor [n_seg]) on the device."""
+    global launch_count
+    import torch
+    if not act.is_cuda or act.dtype != torch.float32 or act.dim() != 1 or not act.is_contiguous():
+        raise ValueError("activations must be a contiguous 1-D float32 CUDA tensor")
+    n = act.shape[0]
+    n_seg = 1 if seg_offsets is None else int(seg_offsets.shape[0]) - 1
+    peaks = torch.empty((max(n, 1),), dtype=torch.int32, device=act.device)
+    counts = torch.zeros((n_seg,), dtype=torch.int32, device=act.device)
+    kern = None
+    if smooth and smooth > 1:
+        kern = torch.from_numpy(np.hamming(int(smooth))).to(act.device)
+    rc = load().mmb_peak_picking(act.data_ptr(), None if seg_offsets is None else seg_offsets.data_ptr(), n_seg, n,
+                                 float(threshold), int(smooth or 0), None if kern is None else kern.data_ptr(),
+                                 int(pre_avg), int(post_avg), int(pre_max), int(post_max), peaks.data_ptr(),
+                                 counts.data_ptr(), _stream(act.device.index))
+    if rc != MMB_OK:
+        raise ValueError("mmb_peak_picking: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_peak_picking failed")
+    launch_count += 2 if n else 1
+    return peaks, counts

@@ -246,6 +246,7 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.mul = p->cfg.mul; fp.add = p->cfg.add; fp.log_mode = p->cfg.log_mode;
   fp.diff_frames = p->cfg.diff_frames; fp.max_bins = p->cfg.diff_max_bins; fp.positive = p->cfg.positive_diffs;
   fp.circular_shift = p->cfg.circular_shift;
+  fp.spec_log_mode = p->cfg.num_bands == 0 ? p->cfg.log_mode : 0;
   fp.out_stft = (float2*)o->stft; fp.ld_stft = o->ld_stft; fp.out_spec = o->spec; fp.ld_spec = o->ld_spec;
   fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
   fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;

@@ -59,6 +59,21 @@ MMB_HD void load_frame_4096(int lane, int c, float2 (&v)[32], const S* x, const 
   }
 }
 
+// log(mul * x + add) with the reference's order of operations and roundings (x *= mul; x += add; log(x),
+// madmom/audio/spectrogram.py:527-534).  mode: 1 log10, 2 none (mul/add only), 3 ln, 4 log2.
+MMB_HD float log_scaled(float x, int mode, float mul, float add) {
+#if defined(__CUDA_ARCH__)
+  const float y = __fadd_rn(__fmul_rn(x, mul), add);
+  if (mode == 1) return __log2f(y) * 0.30102999566398119521f;
+  if (mode == 3) return __log2f(y) * 0.69314718055994530942f;
+  if (mode == 4) return __log2f(y);
+  return y;
+#else
+  const float y = x * mul + add;
+  return mode == 1 ? log10f(y) : mode == 3 ? logf(y) : mode == 4 ? log2f(y) : y;
+#endif
+}
+
 // ------------------------------------------------------------------------------------------ splits
 // Output sink: magnitudes into warp scratch `mag` (always), and optionally complex bins / magnitudes
 // straight to global memory (row pointers, may be null).  `sgn_odd` = -1 when circular_shift is set:
@@ -68,10 +83,12 @@ struct BinSink {
   float2* stft_row;  // global, K complex, or null
   float* spec_row;   // global, K floats, or null
   float sgn_odd;     // +1 or -1
+  int log_mode;      // != 0: the spec output is log(m * mul + add) (LogarithmicSpectrogram of an unfiltered one)
+  float mul, add;
   MMB_HD void put(int k, float re, float im) const {
     const float m = mag_of(re, im);
     mag[k] = m;
-    if (spec_row) spec_row[k] = m;
+    if (spec_row) spec_row[k] = log_mode ? log_scaled(m, log_mode, mul, add) : m;
     if (stft_row) {
       const float s = (k & 1) ? sgn_odd : 1.0f;
       stft_row[k] = make_float2(re * s, im * s);

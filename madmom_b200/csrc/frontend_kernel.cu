@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(warps_per_cta(N) * 32, 1) frontend_kernel(cons
             BinSink oa, ob;
             const long long rowA = tr.out_row + (gA - tr.frame_first), rowB = rowA + 1;
             oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
+            oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
             oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
             ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
             oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(warps_per_cta(N) * 32, 1) frontend_kernel(cons
           const S* x = s_pcm + (int)(frame_start_sample(g, p.hop, N, p.origin) - s_begin);
           BinSink o;
           const long long row = tr.out_row + (g - tr.frame_first);
-          o.mag = my_mag; o.sgn_odd = sgn_odd;
+          o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
           o.stft_row = (p.out_stft && g >= ga) ? p.out_stft + row * p.ld_stft : nullptr;
           o.spec_row = (p.out_spec && g >= ga) ? p.out_spec + row * p.ld_spec : nullptr;
           if (N == 2048) {
@@ -176,13 +177,7 @@ __global__ void __launch_bounds__(warps_per_cta(N) * 32, 1) frontend_kernel(cons
         for (int i = 0; i < ln; ++i) acc = fmaf(mg[st + i], w[i], acc);
         const long long g = g0 + fi;
         if (p.out_filt && g >= ga) p.out_filt[(tr.out_row + (g - tr.frame_first)) * p.ld_filt + b] = acc;
-        float y = acc;
-        if (p.log_mode != 0) {
-          y = __fadd_rn(__fmul_rn(acc, p.mul), p.add);
-          if (p.log_mode == 1) y = fast_log10(y);
-          else if (p.log_mode == 3) y = __log2f(y) * 0.69314718055994530942f;
-          else if (p.log_mode == 4) y = __log2f(y);
-        }
+        const float y = p.log_mode != 0 ? log_scaled(acc, p.log_mode, p.mul, p.add) : acc;
         s_ring[(int)(g & (kRing - 1)) * nb + b] = y;
       }
       __syncthreads();

@@ -43,6 +43,7 @@ struct FrontendParams {
   int32_t max_bins;              // frequency max-filter width (<=1: none)
   int32_t positive;
   int32_t circular_shift;
+  int32_t spec_log_mode;         // log mode applied to the spec output (plans without a filterbank)
   // outputs (device, row-major, leading dimensions in elements; null -> not produced)
   float2* out_stft; int64_t ld_stft;
   float* out_spec;  int64_t ld_spec;

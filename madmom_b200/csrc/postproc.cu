@@ -1,0 +1,220 @@
+// Stages either side of the fused front-end kernel that work on matrices / vectors already in HBM:
+//
+//   mmb_matrix_diff   SpectrogramDifference of an arbitrary (rows, cols) float32 matrix (used for unfiltered
+//                     spectrograms, whose 1024..2048 columns do not fit the fused kernel's shared-memory ring):
+//                     scipy maximum_filter(size=(1, m), mode='reflect') on the lagged row, subtraction, optional
+//                     half-wave rectification, optional row sums.   madmom/audio/spectrogram.py:976-993,
+//                     madmom/features/onsets.py:163-240.
+//   mmb_peak_picking  peak_picking() of madmom/features/onsets.py:875-963 on one or many activation functions:
+//                     optional Hamming smoothing, moving average (scipy uniform_filter, mode='constant'),
+//                     threshold, moving maximum (scipy maximum_filter, mode='constant'), equality test, ordered
+//                     compaction of the surviving frame indices.
+//
+// Both are HBM-bound stencils: every element is read once from DRAM (neighbours come from L1/L2).
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/madmom_b200.h"
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------- matrix diff
+// one warp per output row; lanes stride over columns
+__global__ void __launch_bounds__(256) matrix_diff_kernel(const float* __restrict__ in, int64_t ld_in,
+                                                          float* __restrict__ out, int64_t ld_out,
+                                                          float* __restrict__ odf, int64_t rows, int32_t cols,
+                                                          int64_t seg_rows, int32_t d, int32_t max_bins,
+                                                          int32_t positive) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int64_t local = seg_rows > 0 ? row % seg_rows : row;     // frame index inside its own signal
+  const bool has_prev = local >= d;
+  const float* cur = in + row * ld_in;
+  const float* prev = in + (row - d) * ld_in;
+  const int half = max_bins / 2;
+  float sum = 0.0f;
+  for (int c = lane; c < cols; c += 32) {
+    float v = 0.0f;
+    if (has_prev) {
+      float ref;
+      if (max_bins > 1) {
+        ref = -INFINITY;
+        for (int j = 0; j < max_bins; ++j) {
+          int q = c - half + j;
+          q = q < 0 ? -q - 1 : (q >= cols ? 2 * cols - q - 1 : q);     // 'reflect': (d c b a | a b c d | d c b a)
+          ref = fmaxf(ref, prev[q]);
+        }
+      } else {
+        ref = prev[c];
+      }
+      v = cur[c] - ref;
+      if (positive) v = fmaxf(v, 0.0f);
+    }
+    if (out) out[row * ld_out + c] = v;
+    sum += v;
+  }
+  if (odf) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) odf[row] = sum;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- peak picking
+struct PeakParams {
+  const float* act;
+  const int64_t* seg;      // [n_seg + 1] element offsets of the segments, or null (one segment [0, n))
+  int64_t n;
+  int32_t n_seg;
+  double threshold;
+  int32_t smooth, pre_avg, post_avg, pre_max, post_max;
+  const double* kernel;    // Hamming window of length `smooth` (device), when smooth > 1
+  int32_t* peaks;          // [n]   segment s writes its local indices at peaks[seg[s] ...]
+  int32_t* counts;         // [n_seg]
+};
+
+__device__ __forceinline__ int find_segment(const int64_t* seg, int n_seg, int64_t i) {
+  int lo = 0, hi = n_seg;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (seg[mid] <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// activation value after the optional smoothing: np.convolve(x, hamming(k), 'same') evaluated in float64
+template <typename T>
+__device__ __forceinline__ T smoothed(const PeakParams& p, int64_t s0, int64_t len, int64_t i) {
+  if (p.smooth <= 1) return (T)p.act[s0 + i];
+  // 'same' output i <-> full output i + (k - 1) / 2;   full[m] = sum_j x[m - j] k[j]
+  const int k = p.smooth;
+  const int64_t m = i + (k - 1) / 2;
+  double acc = 0.0;
+  for (int j = 0; j < k; ++j) {
+    const int64_t q = m - j;
+    if (q >= 0 && q < len) acc += (double)p.act[s0 + q] * p.kernel[j];
+  }
+  return (T)acc;
+}
+
+// detections[i] = act[i] * (act[i] >= mov_avg[i] + threshold)          (onsets.py:927-942)
+template <typename T>
+__device__ __forceinline__ T detection(const PeakParams& p, int64_t s0, int64_t len, int64_t i) {
+  if (i < 0 || i >= len) return (T)0;                                   // mode='constant', cval 0
+  const T a = smoothed<T>(p, s0, len, i);
+  const int avg_len = p.pre_avg + p.post_avg + 1;
+  T limit;
+  if (avg_len > 1) {
+    // scipy uniform_filter1d: window [i - n/2 - origin, ... + n), origin = floor((pre - post) / 2), zeros outside,
+    // accumulated in double, divided by n, stored in the array's dtype
+    const int origin = (int)floor((double)(p.pre_avg - p.post_avg) / 2.0);
+    const int64_t w0 = i - avg_len / 2 - origin;
+    double acc = 0.0;
+    for (int j = 0; j < avg_len; ++j) {
+      const int64_t q = w0 + j;
+      if (q >= 0 && q < len) acc += (double)smoothed<T>(p, s0, len, q);
+    }
+    const T avg = (T)(acc / (double)avg_len);
+    limit = avg + (T)p.threshold;
+  } else {
+    limit = (T)p.threshold;
+  }
+  return a >= limit ? a : (T)0;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) peak_flag_kernel(const PeakParams p) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.n) return;
+  int64_t s0 = 0, len = p.n;
+  if (p.seg) {
+    const int s = find_segment(p.seg, p.n_seg, i);
+    s0 = p.seg[s]; len = p.seg[s + 1] - s0;
+  }
+  const int64_t li = i - s0;
+  const T det = detection<T>(p, s0, len, li);
+  int flag = det != (T)0;
+  const int max_len = p.pre_max + p.post_max + 1;
+  if (flag && max_len > 1) {
+    const int origin = (int)floor((double)(p.pre_max - p.post_max) / 2.0);
+    const int64_t w0 = li - max_len / 2 - origin;
+    T mx = det;
+    for (int j = 0; j < max_len; ++j) mx = fmax(mx, detection<T>(p, s0, len, w0 + j));
+    flag = det == mx;
+  }
+  p.peaks[i] = flag;
+}
+
+// ordered in-place compaction: one CTA per segment walks its flags in tiles of blockDim.x
+__global__ void __launch_bounds__(1024) peak_compact_kernel(const PeakParams p) {
+  __shared__ int warp_tot[32];
+  __shared__ int base;
+  const int s = blockIdx.x;
+  const int64_t s0 = p.seg ? p.seg[s] : 0;
+  const int64_t len = (p.seg ? p.seg[s + 1] : p.n) - s0;
+  int32_t* buf = p.peaks + s0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+  for (int64_t t0 = 0; t0 < len; t0 += blockDim.x) {
+    const int64_t i = t0 + threadIdx.x;
+    const int f = (i < len) ? buf[i] : 0;
+    const unsigned m = __ballot_sync(0xffffffffu, f != 0);
+    if (lane == 0) warp_tot[warp] = __popc(m);
+    __syncthreads();                       // every flag of the tile is in a register before anything is written
+    int off = base;
+    for (int w = 0; w < warp; ++w) off += warp_tot[w];
+    if (f) buf[off + __popc(m & ((1u << lane) - 1u))] = (int32_t)i;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tot = 0;
+      for (int w = 0; w < nw; ++w) tot += warp_tot[w];
+      base += tot;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) p.counts[s] = base;
+}
+
+}  // namespace
+
+extern "C" MMB_API int mmb_matrix_diff(const float* in_dev, int64_t ld_in, float* out_dev, int64_t ld_out,
+                                       float* odf_dev, int64_t rows, int32_t cols, int64_t rows_per_signal,
+                                       int32_t diff_frames, int32_t diff_max_bins, int32_t positive_diffs,
+                                       void* stream) {
+  if (!in_dev || (!out_dev && !odf_dev) || rows < 0 || cols <= 0 || diff_frames < 1 || ld_in < cols ||
+      (out_dev && ld_out < cols))
+    return MMB_E_INVALID;
+  if (rows == 0) return MMB_OK;
+  const int warps = 8;
+  const int64_t grid = (rows + warps - 1) / warps;
+  matrix_diff_kernel<<<(unsigned)grid, warps * 32, 0, (cudaStream_t)stream>>>(
+      in_dev, ld_in, out_dev, ld_out, odf_dev, rows, cols, rows_per_signal, diff_frames, diff_max_bins,
+      positive_diffs);
+  return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+}
+
+extern "C" MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg_offsets_dev, int32_t n_segments,
+                                        int64_t n, double threshold, int32_t smooth, const double* smooth_kernel_dev,
+                                        int32_t pre_avg, int32_t post_avg, int32_t pre_max, int32_t post_max,
+                                        int32_t* peaks_dev, int32_t* counts_dev, void* stream) {
+  if (!act_dev || !peaks_dev || !counts_dev || n < 0 || n_segments < 1 || pre_avg < 0 || post_avg < 0 ||
+      pre_max < 0 || post_max < 0 || smooth < 0 || (smooth > 1 && !smooth_kernel_dev) ||
+      (n_segments > 1 && !seg_offsets_dev))
+    return MMB_E_INVALID;
+  PeakParams p;
+  p.act = act_dev; p.seg = seg_offsets_dev; p.n = n; p.n_seg = n_segments; p.threshold = threshold;
+  p.smooth = smooth; p.pre_avg = pre_avg; p.post_avg = post_avg; p.pre_max = pre_max; p.post_max = post_max;
+  p.kernel = smooth_kernel_dev; p.peaks = peaks_dev; p.counts = counts_dev;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n > 0) {
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    // with smoothing the activations are float64 from there on (np.convolve with a float64 kernel)
+    if (smooth > 1) peak_flag_kernel<double><<<grid, 256, 0, st>>>(p);
+    else peak_flag_kernel<float><<<grid, 256, 0, st>>>(p);
+  }
+  peak_compact_kernel<<<n_segments, 1024, 0, st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+}

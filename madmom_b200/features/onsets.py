@@ -1,0 +1,165 @@
+"""Onset detection functions on top of the fused front end, and peak picking on the device.
+
+Mirror of madmom/features/onsets.py: `spectral_flux` (:163-190), `superflux` (:193-240), `SpectralOnsetProcessor`
+(:584-720), `peak_picking` (:875-963), `OnsetPeakPickingProcessor` (:966-1180, offline mode) and
+`madmom.utils.combine_events` (madmom/utils/__init__.py:275-330).
+
+The flux reductions are the row-sum epilogue of the fused kernel; peak picking runs as two small CUDA kernels
+(`mmb_peak_picking`), so an onset pipeline copies only the final handful of frame indices back to the host.
+"""
+import inspect
+
+import numpy as np
+
+from ..processors import Processor, SequentialProcessor
+from ..audio.stft import DeviceResult
+from ..audio.spectrogram import Spectrogram, SpectrogramDifference
+
+
+def _as_spectrogram(spectrogram):
+    if not isinstance(spectrogram, Spectrogram):
+        spectrogram = Spectrogram(spectrogram)
+    return spectrogram
+
+
+def spectral_flux(spectrogram, diff_frames=None):
+    """Sum of the positive lagged differences per frame (madmom/features/onsets.py:163-190)."""
+    diff = SpectrogramDifference(_as_spectrogram(spectrogram), diff_frames=diff_frames, positive_diffs=True)
+    return diff.flux()
+
+
+def superflux(spectrogram, diff_frames=None, diff_max_bins=3):
+    """SuperFlux: spectral flux against a frequency-maximum-filtered lagged frame
+    (madmom/features/onsets.py:193-240)."""
+    diff = SpectrogramDifference(_as_spectrogram(spectrogram), diff_frames=diff_frames,
+                                 diff_max_bins=diff_max_bins, positive_diffs=True)
+    return diff.flux()
+
+
+class SpectralOnsetProcessor(SequentialProcessor):
+    """Signal -> frames -> STFT -> spectrogram [-> filterbank] [-> log] -> onset detection function
+    (madmom/features/onsets.py:584-683).  The whole chain is one kernel launch."""
+    METHODS = ["superflux", "spectral_flux"]
+
+    def __init__(self, onset_method="spectral_flux", **kwargs):
+        from ..audio.signal import SignalProcessor, FramedSignalProcessor
+        from ..audio.stft import ShortTimeFourierTransformProcessor
+        from ..audio.spectrogram import (SpectrogramProcessor, FilteredSpectrogramProcessor,
+                                         LogarithmicSpectrogramProcessor)
+        if not inspect.isfunction(onset_method) and any(odf in onset_method for odf in ("phase", "complex")):
+            kwargs["circular_shift"] = True
+        kwargs["num_channels"] = 1
+        processors = [SignalProcessor(**kwargs), FramedSignalProcessor(**kwargs),
+                      ShortTimeFourierTransformProcessor(**kwargs), SpectrogramProcessor(**kwargs)]
+        if kwargs.get("filterbank") is not None:
+            processors.append(FilteredSpectrogramProcessor(**kwargs))
+        if kwargs.get("log") is not None:
+            processors.append(LogarithmicSpectrogramProcessor(**kwargs))
+        if not inspect.isfunction(onset_method):
+            try:
+                onset_method = globals()[onset_method]
+            except KeyError:
+                raise ValueError("%s not a valid onset detection function, choose %s." % (onset_method,
+                                                                                           self.METHODS))
+        processors.append(onset_method)
+        super(SpectralOnsetProcessor, self).__init__(processors)
+
+
+# ------------------------------------------------------------------------------------------------ peak picking
+def _device_vector(activations):
+    """1-D float32 CUDA tensor of an activation function (device results stay where they are)."""
+    import torch
+    from .._engine import current_device
+    if isinstance(activations, DeviceResult):
+        t = activations.tensor
+    elif isinstance(activations, torch.Tensor):
+        t = activations
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.asarray(activations)))
+    if t.dim() != 1:
+        raise ValueError("`activations` must be a 1D array on the GPU path")       # the 2D case is not offered
+    return t.to(device="cuda:%d" % current_device(), dtype=torch.float32).contiguous()
+
+
+def peak_picking(activations, threshold, smooth=None, pre_avg=0, post_avg=0, pre_max=1, post_max=1):
+    """Frame indices of the peaks of a 1-D activation function (madmom/features/onsets.py:875-963).
+    All lengths are in frames.  Returns a numpy int array like np.nonzero()[0] does in the reference."""
+    from .. import _lib
+    if smooth is None:
+        smooth = 0
+    if isinstance(smooth, np.ndarray):
+        raise NotImplementedError("explicit smoothing kernels are not available on the GPU path")
+    if smooth == 1 or smooth < 0:
+        raise ValueError("can't create a smoothing kernel of size %d" % smooth)
+    act = _device_vector(activations)
+    peaks, counts = _lib.peak_picking(act, threshold, int(smooth), int(pre_avg), int(post_avg), int(pre_max),
+                                      int(post_max))
+    n = int(counts[0].item())
+    return peaks[:n].cpu().numpy().astype(np.int64)
+
+
+def combine_events(events, delta, combine="mean"):
+    """Merge events closer than `delta` (madmom/utils/__init__.py:275-330); a handful of scalars on the host."""
+    delta += 1e-12
+    if len(events) <= 1:
+        return events
+    events = np.array(events, dtype=float)
+    if events.ndim > 1:
+        raise ValueError("only 1-dimensional events supported.")
+    kept = 0
+    left = events[0]
+    for right in events[1:]:
+        if right - left <= delta:
+            if combine == "mean":
+                left = events[kept] = 0.5 * (right + left)
+            elif combine == "left":
+                left = events[kept] = left
+            elif combine == "right":
+                left = events[kept] = right
+            else:
+                raise ValueError("don't know how to combine two events with %s" % combine)
+        else:
+            kept += 1
+            left = events[kept] = right
+    return events[:kept + 1]
+
+
+class OnsetPeakPickingProcessor(Processor):
+    """Offline peak picking of an onset activation function; times in seconds
+    (madmom/features/onsets.py:966-1107).  Online (frame-by-frame) mode is not available on the GPU path."""
+    FPS = 100
+    THRESHOLD = 0.5
+    SMOOTH = 0.
+    PRE_AVG = 0.
+    POST_AVG = 0.
+    PRE_MAX = 0.
+    POST_MAX = 0.
+    COMBINE = 0.03
+    DELAY = 0.
+
+    def __init__(self, threshold=THRESHOLD, smooth=SMOOTH, pre_avg=PRE_AVG, post_avg=POST_AVG, pre_max=PRE_MAX,
+                 post_max=POST_MAX, combine=COMBINE, delay=DELAY, online=False, fps=FPS, **kwargs):
+        if online:
+            raise NotImplementedError("online peak picking is not available on the GPU path")
+        self.threshold = threshold
+        self.smooth = smooth
+        self.pre_avg = pre_avg
+        self.post_avg = post_avg
+        self.pre_max = pre_max
+        self.post_max = post_max
+        self.combine = combine
+        self.delay = delay
+        self.fps = fps
+
+    def process(self, activations, **kwargs):
+        timings = np.array([self.smooth, self.pre_avg, self.post_avg, self.pre_max, self.post_max]) * self.fps
+        timings = np.round(timings).astype(int)
+        onsets = peak_picking(activations, self.threshold, *timings)
+        onsets = onsets.astype(float) / self.fps
+        if self.delay:
+            onsets += self.delay
+        if self.combine:
+            onsets = combine_events(onsets, self.combine, "left")
+        return np.asarray(onsets)
+
+    process_offline = process

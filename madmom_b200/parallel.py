@@ -1,0 +1,119 @@
+"""Multi-GPU sharding of the front end: one process per GPU (torchrun), torch.distributed for the plumbing.
+
+Two cases:
+
+* a batch of tracks: independent units, rank r takes a contiguous block of tracks, NO collective
+  (`shard_tracks`) -- the reference's equivalent is one worker process per file (madmom/processors.py:637-713);
+* one long signal: frames are independent except for the `diff_frames` lag, so rank r takes the contiguous
+  frame range [f_r, f_r+1) with equal sizes ceil(T / R), loads the PCM samples those frames (and their
+  `diff_frames` lead-in frames) touch -- a halo of frame_size/2 + diff_frames*hop samples on the left and
+  frame_size/2 on the right -- recomputes the lead-in rows locally and contributes its (rows, cols) slice to
+  ONE all-gather (NCCL over NVLink on GPUs).  Frame starts always use the GLOBAL frame index in int(i * hop)
+  (madmom/audio/signal.py:917), so the gathered matrix is bit-identical to the unsharded one; this is what
+  `FramedSignal.__getitem__(slice)` (signal.py:1181-1194) means for an integer hop.
+
+The shard arithmetic is pure Python (testable on CPU with the gloo backend); only `LongSignalFrontEnd.run`
+touches the GPU.
+"""
+import numpy as np
+
+from . import recipe as R
+
+
+def shard_tracks(n_tracks, world_size, rank):
+    """Contiguous block [lo, hi) of tracks for `rank`; blocks differ by at most one track."""
+    base, extra = divmod(int(n_tracks), int(world_size))
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+class FrameShard(object):
+    """What one rank needs for its frame range of a long signal."""
+
+    def __init__(self, rank, frame_first, frame_count, rows_per_rank, sample_lo, sample_hi):
+        self.rank = rank
+        self.frame_first = frame_first      # global index of the first output frame
+        self.frame_count = frame_count      # real output frames of this rank (0 for ranks past the end)
+        self.rows_per_rank = rows_per_rank  # rows every rank contributes to the all-gather (zero padded)
+        self.sample_lo = sample_lo          # PCM slice [sample_lo, sample_hi) of the global signal
+        self.sample_hi = sample_hi
+
+    def unit(self):
+        """Unit-table row (include/madmom_b200.h: mmb_track) for the local PCM slice."""
+        return (0, self.sample_hi - self.sample_lo, self.sample_lo, self.frame_first, self.frame_count, 0)
+
+    def __repr__(self):
+        return "FrameShard(rank=%d frames [%d, %d) samples [%d, %d))" % (
+            self.rank, self.frame_first, self.frame_first + self.frame_count, self.sample_lo, self.sample_hi)
+
+
+def frame_shards(num_samples, hop_size, frame_size, world_size, origin=0, diff_frames=0, end="normal"):
+    """[FrameShard] for every rank of `world_size`."""
+    T = R.num_frames(num_samples, hop_size, end)
+    per = -(-T // world_size) if T else 0
+    shards = []
+    for r in range(world_size):
+        f0 = min(r * per, T)
+        f1 = min(f0 + per, T)
+        if f1 > f0:
+            lead = max(f0 - diff_frames, 0)
+            s_lo = max(R.frame_start(lead, frame_size, hop_size, origin), 0)
+            s_hi = min(R.frame_start(f1 - 1, frame_size, hop_size, origin) + frame_size, num_samples)
+            s_hi = max(s_hi, s_lo)
+        else:
+            s_lo = s_hi = 0
+        shards.append(FrameShard(r, f0, f1 - f0, per, s_lo, s_hi))
+    return shards
+
+
+def gather_rows(local, total_rows, group=None):
+    """All-gather equal-sized (rows_per_rank, cols) slices along the rows and drop the padding of the last
+    ranks.  `local` is a torch tensor (CUDA with NCCL, CPU with gloo)."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    full = torch.empty((world * local.shape[0],) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(full, local.contiguous(), group=group)
+    return full[:total_rows]
+
+
+class LongSignalFrontEnd(object):
+    """One long signal split into frame ranges over the ranks of the default process group."""
+
+    def __init__(self, rec, pcm_dtype=np.int16, device=None):
+        import torch
+        from .batch import plan_for
+        self.recipe = rec
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.plan = plan_for(rec, pcm_dtype, self.device)
+        self.pcm_dtype = np.dtype(pcm_dtype)
+
+    def shard(self, num_samples, world_size, rank):
+        rec = self.recipe
+        return frame_shards(num_samples, rec.hop_size, rec.frame_size, world_size,
+                            R.resolve_origin(rec.origin, rec.frame_size), self.plan.diff_frames, rec.end)[rank]
+
+    def run_local(self, pcm_slice, shard, outputs=("diff",)):
+        """Fused kernel on this rank's PCM slice (CUDA tensor holding samples [sample_lo, sample_hi)).
+        Returns {name: (rows_per_rank, cols) tensor}, rows past the rank's frame_count are zero."""
+        import torch
+        from . import _lib
+        units = np.zeros(1, dtype=_lib.TRACK_DTYPE)
+        units[0] = shard.unit()
+        dev = "cuda:%d" % self.device
+        out = {}
+        for n in outputs:
+            shape = (shard.rows_per_rank,) if n == "odf" else (shard.rows_per_rank, self.plan.width(n))
+            out[n] = torch.zeros(shape, dtype=torch.float32, device=dev)
+        if shard.frame_count > 0:
+            self.plan.run(pcm_slice, units, {n: t[:shard.frame_count] for n, t in out.items()})
+        return out
+
+    def run(self, pcm_slice, num_samples, outputs=("diff",), group=None):
+        """Compute this rank's slice and all-gather: every rank returns the full (T, cols) matrices."""
+        import torch.distributed as dist
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        shard = self.shard(num_samples, world, rank)
+        local = self.run_local(pcm_slice, shard, outputs)
+        T = R.num_frames(num_samples, self.recipe.hop_size, self.recipe.end)
+        return {n: gather_rows(t, T, group) for n, t in local.items()}

@@ -1,0 +1,299 @@
+"""GPU parity tests of the drop-in processor layer (madmom_b200.audio.*, madmom_b200.features.onsets) against the
+reference's golden vectors (tests/golden/, produced by the real madmom) and the CPU oracle.  They read like the
+reference's own tests (tests/test_audio_spectrogram.py, tests/test_features_onsets.py).
+Bounds: integers bit-exact; float32 features |gpu - ref| <= 1e-5 + 1e-4 |ref|."""
+import pickle
+
+import numpy as np
+import pytest
+
+from conftest import assert_close
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def sig(sample_pcm):
+    from madmom_b200.audio.signal import Signal
+    return Signal(sample_pcm, sample_rate=44100)
+
+
+def test_spectrogram_stages(sig, ref_sample):
+    from madmom_b200.audio.signal import FramedSignal
+    from madmom_b200.audio.stft import ShortTimeFourierTransform
+    from madmom_b200.audio.spectrogram import (Spectrogram, FilteredSpectrogram, LogarithmicSpectrogram,
+                                               LogarithmicFilteredSpectrogram)
+    rows = ref_sample["rows"]
+    frames = FramedSignal(sig, frame_size=2048, hop_size=441.)
+    stft = ShortTimeFourierTransform(frames)
+    assert stft.shape == (281, 1024) and stft.dtype == np.complex64
+    scale = np.abs(ref_sample["stft_rows"]).max()
+    assert np.abs(np.asarray(stft)[rows] - ref_sample["stft_rows"]).max() <= 2e-6 * scale
+    spec = Spectrogram(stft)
+    assert spec.shape == (281, 1024) and spec.num_bins == 1024 and spec.num_frames == 281
+    # reference: tests/test_audio_spectrogram.py:82-96
+    assert np.allclose(spec[0, :8], [3.15249, 4.00272, 5.66156, 6.30141, 6.02199, 10.84909, 17.83130, 19.44511])
+    assert np.abs(np.asarray(spec)[rows] - ref_sample["spec_rows"]).max() <= 2e-6 * scale
+    assert np.allclose(np.asarray(spec, dtype=np.float64).sum(axis=0), ref_sample["spec_col_sums"], rtol=1e-4,
+                       atol=1e-4)
+    filt = FilteredSpectrogram(spec)
+    assert filt.shape == (281, 81) and filt.filterbank.shape == (1024, 81)
+    assert_close(np.asarray(filt), ref_sample["filt12n"], what="FilteredSpectrogram")
+    logfilt = LogarithmicFilteredSpectrogram(spec)
+    assert_close(np.asarray(logfilt), ref_sample["logfilt12n"], what="LogarithmicFilteredSpectrogram")
+    assert np.allclose(logfilt.bin_frequencies[:3], filt.bin_frequencies[:3])
+    # log of the unfiltered spectrogram (tests/test_audio_spectrogram.py:285-293)
+    logspec = LogarithmicSpectrogram(spec)
+    assert logspec.shape == (281, 1024)
+    assert_close(np.asarray(logspec)[rows], ref_sample["logspec_rows"], what="LogarithmicSpectrogram")
+    # building from anything a Signal can be made of, kwargs travel down the chain
+    lf24 = LogarithmicFilteredSpectrogram(frames, num_bands=24, norm_filters=False)
+    assert_close(np.asarray(lf24), ref_sample["logfilt24"], what="logfilt24")
+
+
+def test_superflux_processor(sig, ref_sample):
+    from madmom_b200.audio.signal import FramedSignalProcessor
+    from madmom_b200.audio.spectrogram import SuperFluxProcessor, SpectrogramDifference
+    proc = SuperFluxProcessor()
+    proc = pickle.loads(pickle.dumps(proc))
+    res = proc(FramedSignalProcessor()(sig))
+    assert isinstance(res, SpectrogramDifference)
+    assert res.shape == (281, 140) and res.diff_frames == 1 and res.diff_max_bins == 3
+    assert_close(np.asarray(res), ref_sample["superflux_diff"], what="SuperFluxProcessor")
+    # tests/test_audio_spectrogram.py:584-591
+    assert np.allclose(res[1, :8], [0.11168772, 0.12317812, 0, 0, 0.03797626, 0.18899226, 0, 0.0903399], atol=1e-5)
+    assert not np.asarray(res)[0].any()
+    again = pickle.loads(pickle.dumps(res))            # results travel through pickle with their host copy
+    assert np.array_equal(np.asarray(again), np.asarray(res))
+    # keep_dims=False and signed differences
+    d2 = SpectrogramDifference(res.spectrogram, diff_frames=2, diff_max_bins=3, positive_diffs=False)
+    assert_close(np.asarray(d2), ref_sample["diff_signed_d2"], what="signed d=2")
+    d2k = SpectrogramDifference(res.spectrogram, diff_frames=2, diff_max_bins=3, keep_dims=False)
+    assert d2k.shape == (279, 140)
+    assert np.array_equal(np.asarray(d2k), np.asarray(d2)[2:])
+
+
+def _multires_chain(mul, ratio):
+    from madmom_b200.processors import ParallelProcessor, SequentialProcessor
+    from madmom_b200.audio.signal import FramedSignalProcessor
+    from madmom_b200.audio.stft import ShortTimeFourierTransformProcessor
+    from madmom_b200.audio.spectrogram import (FilteredSpectrogramProcessor, LogarithmicSpectrogramProcessor,
+                                               SpectrogramDifferenceProcessor)
+    multi = ParallelProcessor([])
+    for frame_size in [1024, 2048, 4096]:
+        frames = FramedSignalProcessor(frame_size=frame_size, fps=100)
+        stft = ShortTimeFourierTransformProcessor()
+        filt = FilteredSpectrogramProcessor(num_bands=6, fmin=30, fmax=17000, norm_filters=True)
+        spec = LogarithmicSpectrogramProcessor(mul=mul, add=1)
+        diff = SpectrogramDifferenceProcessor(diff_ratio=ratio, positive_diffs=True, stack_diffs=np.hstack)
+        multi.append(SequentialProcessor((frames, stft, filt, spec, diff)))
+    return SequentialProcessor((multi, np.hstack))
+
+
+def test_multiresolution_stack(sig, ref_sample):
+    """RNNOnsetProcessor / RNNBeatProcessor pre-processing spelled exactly as the reference does
+    (features/onsets.py:778-791, features/beats.py:93-106) and through MultiFrameProcessor."""
+    from madmom_b200.audio.spectrogram import MultiFrameProcessor
+    on = _multires_chain(5, 0.25)(sig)
+    assert on.shape == (281, 266)
+    assert_close(on, ref_sample["rnn_onset_stack"], what="rnn onset stack")
+    be = _multires_chain(1, 0.5)(sig)
+    assert_close(be, ref_sample["rnn_beat_stack"], what="rnn beat stack")
+    mf = MultiFrameProcessor(mul=5, diff_ratio=0.25)(sig)
+    assert mf.shape == (281, 266) and mf.tensor.is_cuda
+    assert np.array_equal(np.asarray(mf), on)
+
+
+def test_onset_functions_and_peaks(sig, sample_pcm, ref_sample):
+    from madmom_b200.audio.filters import LogarithmicFilterbank
+    from madmom_b200.audio.signal import FramedSignal
+    from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
+    from madmom_b200.features.onsets import (spectral_flux, superflux, SpectralOnsetProcessor, peak_picking,
+                                             OnsetPeakPickingProcessor)
+    spec = Spectrogram(FramedSignal(sig, frame_size=2048, hop_size=441.))
+    # spectral flux of the plain spectrogram (1024 columns: materialise + mmb_matrix_diff)
+    sf = spectral_flux(spec)
+    assert sf.shape == (281,)
+    assert_close(np.asarray(sf), ref_sample["odf_spectralflux_plain"], what="spectral_flux(plain)")
+    assert np.allclose(sf[:4], [0., 100.90121, 74.4442, 40.277565], rtol=1e-4)     # features/onsets.py:636-638
+    lf24 = LogarithmicFilteredSpectrogram(spec, num_bands=24, norm_filters=False)
+    assert_close(np.asarray(superflux(lf24)), ref_sample["odf_superflux_100"], what="superflux")
+    lf12 = LogarithmicFilteredSpectrogram(spec, num_bands=12, norm_filters=False)
+    assert_close(np.asarray(spectral_flux(lf12)), ref_sample["odf_logfiltspecflux"], what="log_filt_spec_flux")
+    # bin/SuperFlux: fps 200 -> fractional hop 220.5, d = 2; onsets bit-exact
+    proc = SpectralOnsetProcessor(onset_method="superflux", fps=200, filterbank=LogarithmicFilterbank, num_bands=24,
+                                  fmin=30, fmax=17000, norm_filters=False, log=np.log10, mul=1, add=1,
+                                  diff_ratio=0.5, diff_max_bins=3, positive_diffs=True)
+    act = proc(sig)
+    assert act.shape == (561,)
+    assert_close(np.asarray(act), ref_sample["odf_superflux_200"], what="SpectralOnsetProcessor superflux")
+    assert np.allclose(np.asarray(act), ref_sample["fixture_act_super_flux"], atol=1e-5)
+    peaks = peak_picking(act, 1.1, None, 30, 0, 2, 10)
+    assert np.array_equal(peaks, ref_sample["peaks_superflux_200"])
+    pp = OnsetPeakPickingProcessor(threshold=1.1, pre_max=0.01, post_max=0.05, pre_avg=0.15, post_avg=0,
+                                   combine=0.03, delay=0, fps=200)
+    onsets = pp(act)
+    assert np.array_equal(onsets, ref_sample["onsets_superflux_200"])
+    assert np.allclose(onsets, ref_sample["fixture_det_super_flux"], atol=1e-5)
+    # bin/LogFiltSpecFlux detections
+    pp = OnsetPeakPickingProcessor(threshold=1.6, pre_max=0.01, post_max=0.05, pre_avg=0.15, post_avg=0,
+                                   combine=0.03, delay=0, fps=100)
+    assert np.array_equal(pp(spectral_flux(lf12)), ref_sample["onsets_logfiltspecflux"])
+
+
+def test_peak_picking_vs_oracle(ref_sample):
+    """Integer output, bit-exact: literals of tests/test_features_onsets.py:233-245 and a parameter sweep against
+    the scipy-based oracle on the reference's fixture and on random activations."""
+    from oracle import frontend as O
+    from madmom_b200 import _lib
+    from madmom_b200.features.onsets import peak_picking
+    act = ref_sample["fixture_act_super_flux"]
+    onsets = peak_picking(act, 1.1)
+    assert list(onsets[:6]) == [2, 10, 17, 48, 55, 80] and len(onsets) == 35
+    assert list(peak_picking(act, 1.1, smooth=3)[:6]) == [2, 10, 17, 24, 48, 55]
+    assert list(peak_picking(act, 1.1, pre_max=2, post_max=10, pre_avg=30)[:6]) == [2, 17, 55, 89, 122, 159]
+    rng = np.random.default_rng(3)
+    noise = (rng.random(4000).astype(np.float32) ** 4) * 3
+    for a in (act, noise):
+        for thr in (0.1, 0.5, 1.1):
+            for smooth in (0, 3, 8):
+                for pre_avg, post_avg in ((0, 0), (30, 0), (5, 7), (0, 9)):
+                    for pre_max, post_max in ((1, 1), (0, 0), (2, 10), (7, 0)):
+                        want = O.peak_picking(a, thr, smooth or None, pre_avg, post_avg, pre_max, post_max)
+                        got = peak_picking(a, thr, smooth, pre_avg, post_avg, pre_max, post_max)
+                        assert np.array_equal(got, want), (thr, smooth, pre_avg, post_avg, pre_max, post_max)
+    # many activation functions in one call (segments), empty segment included
+    lens = [561, 0, 4000, 17, 1]
+    parts = [act, act[:0], noise, noise[100:117], noise[:1]]
+    seg = torch.tensor(np.concatenate(([0], np.cumsum(lens))), dtype=torch.int64, device="cuda")
+    peaks, counts = _lib.peak_picking(torch.from_numpy(np.concatenate(parts)).cuda(), 0.5, 0, 30, 0, 2, 10, seg)
+    peaks, counts = peaks.cpu().numpy(), counts.cpu().numpy()
+    for i, part in enumerate(parts):
+        want = O.peak_picking(part, 0.5, None, 30, 0, 2, 10) if len(part) else np.zeros(0, int)
+        s0 = int(seg[i])
+        assert counts[i] == len(want) and np.array_equal(peaks[s0:s0 + counts[i]], want)
+
+
+def test_frame_slices_and_origins(sig, sample_pcm):
+    """FramedSignal.__getitem__(slice) (signal.py:1181-1194) and literal origins, fractional hop included: the
+    GPU rows equal the oracle's on the same sliced framing."""
+    from oracle import frontend as O
+    from madmom_b200.audio.signal import FramedSignal
+    from madmom_b200.audio.spectrogram import Spectrogram
+    for hop in (441., 220.5):
+        frames = FramedSignal(sig, frame_size=2048, hop_size=hop)
+        whole = np.asarray(Spectrogram(frames))
+        part = frames[10:50]
+        assert part.num_frames == 40 and part.origin == int(0 - hop * 10)
+        got = np.asarray(Spectrogram(part))
+        fr = O.framed(sample_pcm, 2048, hop, origin=part.origin, n_frames=40)
+        ref = O.spec(O.stft(fr, O.fft_window(np.hanning, 2048, np.int16)))
+        assert np.abs(got - ref).max() <= 2e-6 * np.abs(ref).max()
+        if hop == 441.:
+            assert np.array_equal(got, whole[10:50])
+    for origin in ("online", "stream"):
+        frames = FramedSignal(sig, frame_size=2048, hop_size=441., origin=origin)
+        got = np.asarray(Spectrogram(frames))
+        fr = O.framed(sample_pcm, 2048, 441., origin=origin)
+        ref = O.spec(O.stft(fr, O.fft_window(np.hanning, 2048, np.int16)))
+        assert np.abs(got - ref).max() <= 2e-6 * np.abs(ref).max()
+
+
+def test_float_signal_window_none_and_mel(sample_pcm):
+    from oracle import frontend as O
+    from madmom_b200.audio.filters import MelFilterbank
+    from madmom_b200.audio.signal import Signal, FramedSignal
+    from madmom_b200.audio.stft import ShortTimeFourierTransform
+    from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
+    x = (sample_pcm.astype(np.float64) / 32767.).astype(np.float32)
+    frames = FramedSignal(Signal(x, sample_rate=44100), frame_size=1024, hop_size=441.)
+    got = np.asarray(Spectrogram(ShortTimeFourierTransform(frames, window=None)))
+    ref = O.spec(O.stft(O.framed(x, 1024, 441.), None))
+    assert np.abs(got - ref).max() <= 2e-6 * np.abs(ref).max()
+    # Mel filterbank with duplicate low bands + natural log (CNNOnsetProcessor front end, onsets.py:838-871)
+    lf = LogarithmicFilteredSpectrogram(frames, filterbank=MelFilterbank, num_bands=80, fmin=27.5, fmax=16000,
+                                        norm_filters=True, unique_filters=False, log=np.log, add=2.220446049250313e-16)
+    S = O.spec(O.stft(O.framed(x, 1024, 441.), O.fft_window(np.hanning, 1024, np.float32)))
+    want = O.logarithmic(O.filtered(S, np.asarray(lf.filterbank)), 1., np.float32(2.220446049250313e-16), np.log)
+    assert lf.shape == want.shape == (281, 80)
+    # log(x + eps) of tiny band energies amplifies relative FFT rounding: compare where the band is not ~0
+    big = O.filtered(S, np.asarray(lf.filterbank)) > 1e-6
+    assert_close(np.asarray(lf)[big], want[big], rtol=1e-4, atol=2e-5, what="mel ln")
+
+
+def test_errors(sig):
+    from madmom_b200.audio.signal import Signal, FramedSignal
+    from madmom_b200.audio.stft import ShortTimeFourierTransform
+    from madmom_b200.audio.spectrogram import FilteredSpectrogram, SpectrogramDifferenceProcessor, Spectrogram
+    stereo = Signal(np.zeros((5000, 2), np.int16), sample_rate=44100)
+    with pytest.raises(ValueError):
+        ShortTimeFourierTransform(FramedSignal(stereo))              # stft.py:81-84
+    with pytest.raises(TypeError):
+        FilteredSpectrogram(FramedSignal(sig), filterbank="nope")    # spectrogram.py:378-380
+    with pytest.raises(ValueError):
+        FramedSignal(sig, end="bogus")                               # signal.py:1153-1155
+    with pytest.raises(NotImplementedError):
+        ShortTimeFourierTransform(FramedSignal(sig, frame_size=512))
+    with pytest.raises(NotImplementedError):
+        ShortTimeFourierTransform(FramedSignal(sig), fft_size=4096)
+    with pytest.raises(NotImplementedError):
+        SpectrogramDifferenceProcessor()(Spectrogram(FramedSignal(sig)).filter(), reset=False)
+    # mono down-mix like the reference (mean cast back to int16) then the GPU path
+    mixed = Signal(np.stack((np.asarray(sig), np.asarray(sig) // 2), axis=1), sample_rate=44100, num_channels=1)
+    assert mixed.ndim == 1 and Spectrogram(FramedSignal(mixed)).shape == (281, 1024)
+    before = np.asarray(sig).copy()
+    np.asarray(Spectrogram(FramedSignal(sig)))
+    assert np.array_equal(before, np.asarray(sig))                   # inputs are never mutated
+
+
+def test_long_signal_shards_on_one_gpu():
+    """The per-rank work of the long-signal path (parallel.LongSignalFrontEnd.run_local) for 1, 2, 4 and 8 ranks,
+    executed one rank after the other on this GPU and concatenated like the all-gather does, is bit-identical to
+    the unsharded launch (fractional hop and d = 2 included)."""
+    from madmom_b200 import parallel, recipe as R
+    from madmom_b200.batch import BatchFrontEnd
+    from madmom_b200.synth import make_track
+    x = make_track(11, num_samples=400003)
+    for rec in (R.SUPERFLUX, R.SUPERFLUX_200):
+        whole = BatchFrontEnd(rec).run_device(torch.from_numpy(x).cuda(), [len(x)], ("diff", "odf"))
+        T = whole["diff"].shape[0]
+        fe = parallel.LongSignalFrontEnd(rec)
+        for world in (1, 2, 4, 8):
+            parts = {"diff": [], "odf": []}
+            for rank in range(world):
+                sh = fe.shard(len(x), world, rank)
+                local = fe.run_local(torch.from_numpy(x[sh.sample_lo:sh.sample_hi].copy()).cuda(), sh,
+                                     ("diff", "odf"))
+                for k in parts:
+                    parts[k].append(local[k])
+            for k in parts:
+                full = torch.cat(parts[k])[:T]
+                assert torch.equal(full, whole[k]), (rec.hop_size, world, k)
+
+
+def test_batch_front_end_stack_and_host_path():
+    from oracle import frontend as O
+    from madmom_b200 import recipe as R
+    from madmom_b200.batch import BatchFrontEnd
+    from madmom_b200.synth import make_track
+    tracks = [make_track(1000 + i, num_samples=n) for i, n in enumerate((30000, 44100, 12345))]
+    pcm = np.concatenate(tracks)
+    lens = [len(t) for t in tracks]
+    fe = BatchFrontEnd(R.RNN_BEAT)
+    out = fe.run_device(torch.from_numpy(pcm).cuda(), lens, ("stack",))["stack"].cpu().numpy()
+    assert out.shape[1] == 266
+    r0 = 0
+    for x in tracks:
+        cols = []
+        for N in (1024, 2048, 4096):
+            st = O.run_recipe(x, dict(frame_size=N, hop_size=441., num_bands=6, norm_filters=True, mul=1, add=1,
+                                      diff_ratio=0.5, positive_diffs=True), stages=True)
+            cols += [st["log"], st["diff"]]
+        want = np.hstack(cols)
+        assert_close(out[r0:r0 + len(want)], want, what="batched multi-resolution stack")
+        r0 += len(want)
+    assert r0 == out.shape[0]
+    host = fe.run_host(pcm, lens, ("stack",))["stack"].numpy()
+    assert np.array_equal(host, out)

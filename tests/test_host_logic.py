@@ -1,0 +1,209 @@
+"""CPU tests of the host side of the product: integer framing logic, filterbank construction, the processor
+plumbing, the lazy result objects (metadata only, nothing is computed without a GPU) and the C-ABI library's
+export table.  No compute call is made here."""
+import ctypes
+import os
+import pickle
+import re
+
+import numpy as np
+import pytest
+
+from oracle import frontend as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ------------------------------------------------------------------ C ABI
+def test_library_exports_every_declared_symbol():
+    from madmom_b200 import _lib
+    from madmom_b200.build import build_library
+    build_library()
+    lib = _lib.load()
+    header = open(os.path.join(ROOT, "include", "madmom_b200.h")).read()
+    declared = set(re.findall(r"MMB_API\s+[\w\s\*]+?\b(mmb_\w+)\s*\(", header))
+    assert declared, "no declarations found in the header"
+    assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
+    for name in declared:
+        assert getattr(lib, name) is not None
+    assert lib.mmb_version() >= 100
+    # struct layouts of the binding match the header (field order / sizes)
+    assert ctypes.sizeof(_lib.Track) == 48 and _lib.TRACK_DTYPE.itemsize == 48
+    assert ctypes.sizeof(_lib.Outputs) == 11 * 8
+
+
+def test_framing_helpers_in_library(ref_framing):
+    from madmom_b200 import _lib
+    for n, hop, end, want in ref_framing["num_frames_cases"]:
+        assert _lib.num_frames(int(n), hop, "extend" if end else "normal") == int(want)
+    for i in (0, 1, 3, 560, 3599999):
+        for hop in (441., 220.5, 441.3):
+            assert _lib.frame_start(i, 2048, hop, 7) == O.frame_start(i, 2048, hop, 7)
+    with pytest.raises(ValueError):
+        _lib.num_frames(10, 441., "bogus")
+
+
+# ------------------------------------------------------------------ recipe / framing / filters vs the pinned oracle
+def test_recipe_scalars(ref_framing):
+    from madmom_b200 import recipe as R
+    for N, hop, ratio, want in ref_framing["diff_frames_cases"]:
+        assert R.diff_frames(ratio, hop, int(N)) == int(want)
+    for n, hop, end, want in ref_framing["num_frames_cases"]:
+        assert R.num_frames(int(n), hop, "extend" if end else "normal") == int(want)
+    assert [R.resolve_origin(o, 2048) for o in ("offline", "online", "stream", 5)] == [0, 1023, -1024, 5]
+    assert np.array_equal(R.fft_window(np.hanning, 2048, np.int16), O.fft_window(np.hanning, 2048, np.int16))
+    assert np.array_equal(R.fft_window(None, 16, np.int16), np.ones(16) / 32767.)
+    assert np.array_equal(R.fft_window(None, 16, np.float32), np.ones(16))
+    assert R.SUPERFLUX.resolved_diff_frames() == 1 and R.SUPERFLUX_200.resolved_diff_frames() == 2
+    assert [r.resolved_diff_frames() for r in R.RNN_ONSET] == [1, 2, 3]
+    assert [r.resolved_diff_frames() for r in R.RNN_BEAT] == [1, 1, 2]
+    assert [r.build_filterbank().shape[1] for r in R.RNN_BEAT] == [39, 45, 49]
+
+
+@pytest.mark.parametrize("N", [1024, 2048, 4096])
+@pytest.mark.parametrize("bpo,norm", [(6, True), (12, False), (12, True), (24, False)])
+def test_product_filterbank_bit_exact(ref_filterbanks, N, bpo, norm):
+    from madmom_b200.audio.filters import LogarithmicFilterbank
+    from madmom_b200.recipe import fft_frequencies
+    fb = LogarithmicFilterbank(fft_frequencies(N // 2, 44100), bpo, norm_filters=norm)
+    key = "N%d_b%d_%s" % (N, bpo, "norm" if norm else "raw")
+    s, l, w = fb.band_table()
+    assert np.array_equal(s, ref_filterbanks[key + "_start"])
+    assert np.array_equal(l, ref_filterbanks[key + "_len"])
+    assert np.array_equal(w, ref_filterbanks[key + "_w"])
+    assert np.array_equal(fb.center_frequencies, ref_filterbanks[key + "_center"])
+    back = pickle.loads(pickle.dumps(fb))
+    assert np.array_equal(back, fb) and np.array_equal(back.bin_frequencies, fb.bin_frequencies)
+
+
+def test_product_filterbank_misc(ref_filterbanks):
+    from madmom_b200.audio import filters as F
+    fb = F.LogarithmicFilterbank(O.fft_frequencies(1024, 44100), 12, unique_filters=False)
+    assert np.array_equal(np.asarray(fb), ref_filterbanks["N2048_b12_norm_nonunique_dense"])
+    # reference literals: tests/test_audio_filters.py:224-233, 396-421, 1051-1074
+    assert len(F.log_frequencies(6, 30, 17000)) == 55
+    assert np.allclose(F.log_frequencies(1, 100, 1000, 441), [110.25, 220.5, 441., 882.])
+    assert np.allclose(F.frequencies2bins([0, 1, 2, 3, 4, 5], [0, 2, 4]), [0, 1, 1, 2, 2, 2])
+    assert np.allclose(F.frequencies2bins([0, 1, 2, 3, 4, 5], [0, 2, 4], unique_bins=True), [0, 1, 2])
+    fb = F.LogarithmicFilterbank(np.arange(0, 20000, 20), 12)
+    assert fb.shape == (1000, 81) and fb.num_bands == 81 and fb.num_bins == 1000
+    assert np.allclose(fb.min(), 0) and np.allclose(fb.max(), 1)
+    mel = F.MelFilterbank(O.fft_frequencies(1024, 44100), 40)
+    assert mel.shape[0] == 1024 and mel.shape[1] <= 40
+    with pytest.raises(TypeError):
+        F.Filterbank(np.zeros(10), np.arange(10))
+    with pytest.raises(ValueError):
+        F.Filterbank(np.zeros((10, 2)), np.arange(9))
+
+
+def test_signal_and_framed_signal(sample_pcm, ref_sample):
+    from madmom_b200.audio.signal import Signal, FramedSignal, FramedSignalProcessor
+    sig = Signal(sample_pcm, sample_rate=44100)
+    assert sig.num_samples == 123481 and sig.num_channels == 1 and sig.sample_rate == 44100
+    assert np.isclose(sig.length, 2.8)
+    frames = FramedSignal(sig)
+    assert frames.shape == (281, 2048) and len(frames) == 281 and frames.ndim == 2
+    assert frames.hop_size == 441. and frames.fps == 100. and frames.origin == 0
+    for r, want in zip(ref_sample["rows"], ref_sample["frames_rows"]):
+        assert np.array_equal(frames[int(r)], want)
+    assert np.array_equal(frames[-1], frames[280])
+    with pytest.raises(IndexError):
+        frames[281]
+    with pytest.raises(ValueError):
+        frames[::2]
+    with pytest.raises(TypeError):
+        frames["a"]
+    f200 = FramedSignalProcessor(frame_size=2048, fps=200)(sig)
+    assert f200.num_frames == 561 and f200.hop_size == 220.5
+    sl = f200[3:10]
+    assert sl.num_frames == 7 and sl.origin == int(-220.5 * 3)
+    assert FramedSignal(sig, origin="online").origin == 1023 and FramedSignal(sig, origin="stream").origin == -1024
+    assert FramedSignal(sig, end="extend").num_frames == O.num_frames(len(sample_pcm), 441., "extend")
+    assert FramedSignalProcessor(fps=100)(sig, fps=50).hop_size == 882.        # process() kwargs override
+    back = pickle.loads(pickle.dumps(frames))
+    assert back.num_frames == 281 and np.array_equal(np.asarray(back.signal), sample_pcm)
+    stereo = Signal(np.stack((sample_pcm, sample_pcm // 2), axis=1), sample_rate=44100)
+    assert stereo.num_channels == 2 and FramedSignal(stereo).shape == (281, 2048, 2)
+    mono = Signal(stereo, num_channels=1)
+    assert np.array_equal(np.asarray(mono), np.mean(np.asarray(stereo), axis=-1).astype(np.int16))
+
+
+def test_processor_plumbing(tmp_path):
+    from madmom_b200.processors import Processor, SequentialProcessor, ParallelProcessor
+
+    class Add(Processor):
+        def __init__(self, k):
+            self.k = k
+
+        def process(self, data, scale=1, **kwargs):
+            return data + self.k * scale
+
+    seq = SequentialProcessor([Add(1), [Add(2), lambda x: x * 10], None])
+    assert isinstance(seq[1], SequentialProcessor) and len(seq) == 3
+    assert seq(1) == 40 and seq(1, scale=2) == 70                  # kwargs reach Processors, not bare callables
+    par = ParallelProcessor([Add(1), Add(2)], num_threads=4)
+    assert par(1) == [2, 3]
+    assert SequentialProcessor((par, sum))(1) == 5
+    seq.append(Add(5))
+    assert seq(1) == 45
+    path = str(tmp_path / "p.pkl")
+    from madmom_b200.audio.signal import FramedSignalProcessor
+    FramedSignalProcessor(frame_size=1024, fps=50).dump(path)
+    back = Processor.load(path)
+    assert isinstance(back, FramedSignalProcessor) and back.frame_size == 1024 and back.fps == 50
+
+
+def test_lazy_results_metadata_without_gpu(sample_pcm):
+    """Constructing the whole chain allocates nothing and needs no GPU; the attribute graph the reference's
+    consumers walk is there (spectrogram.py:1114-1118, onsets.py:236)."""
+    from madmom_b200.audio.signal import Signal, FramedSignalProcessor
+    from madmom_b200.audio.spectrogram import (SuperFluxProcessor, SpectrogramDifferenceProcessor,
+                                               LogarithmicFilteredSpectrogramProcessor, MultiFrameProcessor)
+    from madmom_b200.features.onsets import SpectralOnsetProcessor, superflux
+    sig = Signal(sample_pcm, sample_rate=44100)
+    res = SuperFluxProcessor()(FramedSignalProcessor()(sig))
+    assert res.shape == (281, 140) and res.diff_frames == 1 and res.positive_diffs and res.diff_max_bins == 3
+    spec = res.spectrogram
+    assert spec.shape == (281, 140) and spec.mul == 1 and spec.add == 1
+    assert spec.filterbank.shape == (1024, 140) and len(spec.bin_frequencies) == 140
+    assert spec.stft.frames.hop_size == 441. and spec.stft.frames.frame_size == 2048
+    assert spec.stft.frames.signal.sample_rate == 44100 and spec.stft.window.shape == (2048,)
+    assert spec.stft.shape == (281, 1024) and len(spec.stft.bin_frequencies) == 1024
+    assert np.array_equal(spec.stft.fft_window, O.fft_window(np.hanning, 2048, np.int16))
+    assert res._tensor is None and "lazy" in repr(res)
+    lf = LogarithmicFilteredSpectrogramProcessor(num_bands=6, mul=5)(FramedSignalProcessor(frame_size=4096)(sig))
+    st = SpectrogramDifferenceProcessor(diff_ratio=0.25, positive_diffs=True, stack_diffs=np.hstack)(lf)
+    assert st.shape == (281, 98) and st.diff_frames == 3
+    proc = SpectralOnsetProcessor(onset_method="superflux", fps=200, num_bands=24, log=np.log10)
+    assert proc.processors[-1] is superflux
+    with pytest.raises(ValueError):
+        SpectralOnsetProcessor(onset_method="nope")
+    for p in (SuperFluxProcessor(), MultiFrameProcessor(), proc, SpectrogramDifferenceProcessor()):
+        pickle.loads(pickle.dumps(p))
+
+
+def test_no_cpu_fallback(sample_pcm, monkeypatch):
+    """Without a CUDA device every compute access fails loudly (there is no CPU path to fall back to)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("needs a machine without a GPU")
+    from madmom_b200 import _lib
+    from madmom_b200.audio.signal import Signal, FramedSignal
+    from madmom_b200.audio.spectrogram import Spectrogram
+    spec = Spectrogram(FramedSignal(Signal(sample_pcm, sample_rate=44100)))
+    with pytest.raises(_lib.LibraryError):
+        np.asarray(spec)
+    monkeypatch.setattr(_lib, "LIBPATH", "/nonexistent/libmadmom_b200.so")
+    monkeypatch.setattr(_lib, "_lib", None)
+    with pytest.raises(_lib.LibraryError):
+        _lib.load()
+
+
+def test_product_does_not_import_the_oracle():
+    import subprocess
+    import sys
+    code = ("import sys; import madmom_b200, madmom_b200.batch, madmom_b200.audio.spectrogram, "
+            "madmom_b200.features.onsets, madmom_b200.parallel; "
+            "bad = [m for m in sys.modules if m == 'oracle' or m.startswith('oracle.') or m.startswith('scipy.fft')]; "
+            "sys.exit(1 if bad else 0)")
+    assert subprocess.call([sys.executable, "-c", code], cwd=ROOT) == 0

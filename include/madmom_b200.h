@@ -155,6 +155,11 @@ MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg_offsets_de
  * best of 5, CUDA events).  The front end is FP32-pipe bound; bench.py reports its roofline against this. */
 MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops);
 
+/* Instruction-rate probes behind the issue-slot roofline in DESIGN.md: which = 1 FFMA with three register
+ * operands, 2 FADD, 3 FMUL+FADD pairs, 4 LDS.64 + 2 FFMA.  *ginst_per_s = 1e9 thread-level FP instructions
+ * per second over the whole device. */
+MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -60,6 +60,7 @@ EXPORTS = {
     "mmb_host_alloc": (c_i32, [ctypes.POINTER(c_vp), c_i64]),
     "mmb_host_free": (c_i32, [c_vp]),
     "mmb_measure_fp32_peak": (c_i32, [c_i32, ctypes.POINTER(c_f64)]),
+    "mmb_rate_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
     "mmb_matrix_diff": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i32, c_i64, c_i32, c_i32, c_i32, c_vp]),
     "mmb_peak_picking": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp,
                                  c_vp, c_vp]),

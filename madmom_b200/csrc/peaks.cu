@@ -51,3 +51,71 @@ extern "C" MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops) {
   *tflops = best;
   return MMB_OK;
 }
+
+// ---- instruction-rate probes used to build the issue-slot roofline of the front end --------
+// which: 0 FFMA with constant-bank operands (same as mmb_measure_fp32_peak), 1 FFMA with three register
+// operands, 2 FADD register-register, 3 FMUL+FADD pairs (butterfly-like), 4 LDS.64 + 2 FFMA (shared-memory fed)
+namespace {
+template <int WHICH>
+__global__ void __launch_bounds__(256) rate_probe(float* out, int iters, float a, float b) {
+  __shared__ float2 sm[512];
+  constexpr int ILP = 8;
+  float acc[ILP], x[ILP], y[ILP];
+#pragma unroll
+  for (int i = 0; i < ILP; ++i) {
+    acc[i] = (float)(threadIdx.x + i); x[i] = a + 1e-7f * (float)(i + threadIdx.x); y[i] = b * (float)(i + 1);
+  }
+  sm[threadIdx.x] = make_float2(a, b); sm[threadIdx.x + 256] = make_float2(b, a);
+  __syncthreads();
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < ILP; ++i) {
+      if (WHICH == 1) acc[i] = fmaf(acc[i], x[i], y[i]);
+      else if (WHICH == 2) acc[i] = acc[i] + x[i];
+      else if (WHICH == 3) { const float t = acc[i] * x[i]; acc[i] = t + y[(i + 1) % ILP]; }
+      else if (WHICH == 4) {
+        const float2 w = sm[(threadIdx.x + 32 * i + it) & 511];
+        acc[i] = fmaf(acc[i], w.x, w.y); acc[i] = fmaf(acc[i], x[i], w.x);
+      }
+    }
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < ILP; ++i) s += acc[i];
+  if (s == 123.456f) out[0] = s;
+}
+}  // namespace
+
+// result: warp-level FP instructions per clock per SM at the current clock estimate is left to the caller;
+// *ginst_per_s receives 1e9 thread-level FP instructions per second (whole device).
+extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s) {
+  if (!ginst_per_s || which < 1 || which > 4) return MMB_E_INVALID;
+  if (cudaSetDevice(device) != cudaSuccess) return MMB_E_CUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return MMB_E_CUDA;
+  float* d = nullptr;
+  if (cudaMalloc(&d, 4) != cudaSuccess) return MMB_E_CUDA;
+  const int iters = 1 << 14, grid = prop.multiProcessorCount * 8;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  double best = 0.0;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(e0);
+    if (which == 1) rate_probe<1><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 2) rate_probe<2><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 3) rate_probe<3><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else rate_probe<4><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return MMB_E_CUDA; }
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double per_iter = (which == 3 || which == 4) ? 2.0 : 1.0;      // FP instructions per chain step
+    const double n = per_iter * 8.0 * (double)iters * 256.0 * grid;
+    const double r = n / (ms * 1e-3) / 1e9;
+    if (rep > 0 && r > best) best = r;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(d);
+  *ginst_per_s = best;
+  return MMB_OK;
+}

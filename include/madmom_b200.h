@@ -100,6 +100,7 @@ typedef struct mmb_outputs {
 typedef struct mmb_plan_info {
   int32_t frame_size, num_bins, num_bands, chunk_frames;
   int32_t smem_bytes, ctas_per_sm, num_sms, frames_per_round;
+  int32_t warps;           /* warps per CTA chosen for this plan (shared-memory budget of one SM) */
 } mmb_plan_info;
 
 MMB_API int mmb_version(void);

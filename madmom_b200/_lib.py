@@ -42,7 +42,7 @@ class Outputs(ctypes.Structure):
 
 class PlanInfo(ctypes.Structure):
     _fields_ = [(n, c_i32) for n in ("frame_size", "num_bins", "num_bands", "chunk_frames", "smem_bytes",
-                                     "ctas_per_sm", "num_sms", "frames_per_round")]
+                                     "ctas_per_sm", "num_sms", "frames_per_round", "warps")]
 
 
 EXPORTS = {

@@ -1,6 +1,7 @@
 // C ABI of libmadmom_b200.so (see include/madmom_b200.h).  Host-side plan construction: twiddle tables
 // are generated in float64 and rounded once to float32; the fft_window is scaled by 0.5 (exact) because
 // the kernel's real-FFT split omits that factor.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -31,12 +32,15 @@ struct mmb_plan {
   int span_cap = 0;
   int sample_bytes = 2;
   int smem_bytes = 0;
-  int ctas_per_sm = 0;
+  int warps = 0;
+  int ring_rows = 0;
   int chunk_frames = 0;
+  int n_passes = 0, n_pieces = 0, w_floats = 0;
   float* d_win = nullptr;
   float2 *d_tw1 = nullptr, *d_tw2k = nullptr, *d_tw4k = nullptr;
-  int32_t *d_bstart = nullptr, *d_blen = nullptr, *d_bwoff = nullptr;
-  float* d_w = nullptr;
+  mmb::FbPass* d_pass = nullptr;
+  float* d_fbw = nullptr;
+  int32_t *d_fbstart = nullptr, *d_fbpid = nullptr, *d_pstart = nullptr;
 };
 
 struct mmb_layout {
@@ -45,6 +49,7 @@ struct mmb_layout {
   int32_t n = 0;
   int32_t total_chunks = 0;
   int64_t total_rows = 0;
+  int64_t pcm_extent = 0;     // max over units of pcm_offset + pcm_len
 };
 
 extern "C" int mmb_version(void) { return MMB_VERSION; }
@@ -72,10 +77,59 @@ static cudaError_t upload(T** dst, const std::vector<T>& src) {
 extern "C" int mmb_plan_destroy(mmb_plan* p) {
   if (!p) return MMB_OK;
   cudaFree(p->d_win); cudaFree(p->d_tw1); cudaFree(p->d_tw2k); cudaFree(p->d_tw4k);
-  cudaFree(p->d_bstart); cudaFree(p->d_blen); cudaFree(p->d_bwoff); cudaFree(p->d_w);
+  cudaFree(p->d_pass); cudaFree(p->d_fbw); cudaFree(p->d_fbstart); cudaFree(p->d_fbpid); cudaFree(p->d_pstart);
   delete p;
   return MMB_OK;
 }
+
+// Per-warp filterbank schedule (frontend_params.h: FbPass).  Bands are cut into pieces of at most kPieceBins
+// bins, pieces are sorted by length (longest first) and dealt to the 32 lanes pass by pass; the weights of a pass
+// are stored [iteration][lane] and zero-padded to the pass's longest piece.
+namespace {
+struct FbSchedule {
+  std::vector<mmb::FbPass> pass;
+  std::vector<float> w;
+  std::vector<int32_t> start, pid, pstart;
+  int n_pieces = 0;
+};
+struct Piece { int start, len, id; const float* w; };
+
+void build_schedule(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, FbSchedule& s) {
+  const int B = cfg->num_bands;
+  std::vector<Piece> pieces;
+  s.pstart.assign(B + 1, 0);
+  for (int b = 0; b < B; ++b) {
+    const int len = cfg->band_len[b];
+    const int n = len > 0 ? (len + mmb::kPieceBins - 1) / mmb::kPieceBins : 0;
+    int at = 0;
+    for (int j = 0; j < n; ++j) {
+      const int l = len / n + (j < len % n ? 1 : 0);
+      pieces.push_back(Piece{cfg->band_start[b] + at, l, (int)pieces.size(), cfg->band_weights + woff[b] + at});
+      at += l;
+    }
+    s.pstart[b + 1] = (int32_t)pieces.size();
+  }
+  s.n_pieces = (int)pieces.size();
+  std::stable_sort(pieces.begin(), pieces.end(), [](const Piece& x, const Piece& y) { return x.len > y.len; });
+  const int n_passes = (s.n_pieces + 31) / 32;
+  s.start.assign(n_passes * 32, 0);
+  s.pid.assign(n_passes * 32, s.n_pieces);          // idle lanes dump into the spare slot
+  for (int ps = 0; ps < n_passes; ++ps) {
+    const int iters = pieces[ps * 32].len;
+    const int off = (int)s.w.size();
+    s.pass.push_back(mmb::FbPass{iters, off});
+    s.w.resize(off + (size_t)iters * 32, 0.0f);
+    for (int l = 0; l < 32 && ps * 32 + l < s.n_pieces; ++l) {
+      const Piece& pc = pieces[ps * 32 + l];
+      int st = pc.start, lead = 0;
+      if (st + iters > K) { lead = st + iters - K; st -= lead; }      // keep every read inside the K magnitudes
+      s.start[ps * 32 + l] = st;
+      s.pid[ps * 32 + l] = pc.id;
+      for (int i = 0; i < pc.len; ++i) s.w[off + (size_t)(i + lead) * 32 + l] = pc.w[i];
+    }
+  }
+}
+}  // namespace
 
 extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   if (!cfg || !out) return fail(MMB_E_INVALID, "null argument");
@@ -133,28 +187,38 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
     const double a = -2.0 * PI * (double)(2 * j + 1) / 4096.0;
     tw4k[j] = make_float2((float)std::cos(a), (float)std::sin(a));
   }
-  std::vector<int32_t> bstart(cfg->band_start, cfg->band_start + cfg->num_bands);
-  std::vector<int32_t> blen(cfg->band_len, cfg->band_len + cfg->num_bands);
-  std::vector<float> w(cfg->band_weights, cfg->band_weights + nnz);
+  FbSchedule sch;
+  build_schedule(cfg, K, woff, sch);
+  p->n_passes = (int)sch.pass.size(); p->n_pieces = sch.n_pieces; p->w_floats = (int)sch.w.size();
   if ((e = upload(&p->d_win, win)) != cudaSuccess || (e = upload(&p->d_tw1, tw1)) != cudaSuccess ||
       (e = upload(&p->d_tw2k, tw2k)) != cudaSuccess || (e = upload(&p->d_tw4k, tw4k)) != cudaSuccess ||
-      (e = upload(&p->d_bstart, bstart)) != cudaSuccess || (e = upload(&p->d_blen, blen)) != cudaSuccess ||
-      (e = upload(&p->d_bwoff, woff)) != cudaSuccess || (e = upload(&p->d_w, w)) != cudaSuccess) {
+      (e = upload(&p->d_pass, sch.pass)) != cudaSuccess || (e = upload(&p->d_fbw, sch.w)) != cudaSuccess ||
+      (e = upload(&p->d_fbstart, sch.start)) != cudaSuccess || (e = upload(&p->d_fbpid, sch.pid)) != cudaSuccess ||
+      (e = upload(&p->d_pstart, sch.pstart)) != cudaSuccess) {
     mmb_plan_destroy(p);
     return cuda_fail(e, "plan constant upload");
   }
-  // ---- shared-memory budget: the staged PCM span of one round
-  const int fpr = mmb::frames_per_round(N);
-  p->span_cap = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N) + 7) & ~7;
-  const mmb::SmemLayout L = mmb::smem_layout(N, cfg->num_bands, nnz, p->span_cap, p->sample_bytes);
-  p->smem_bytes = L.total;
-  if (p->smem_bytes > (int)prop.sharedMemPerBlockOptin) {
+  // ---- warps per CTA: as many as the shared-memory budget of one SM allows (one persistent CTA per SM)
+  const int align_elems = 16 / p->sample_bytes;
+  p->warps = 0;
+  for (int w = mmb::kMaxWarps; w >= 1; --w) {
+    const int fpr = mmb::frames_per_round(N, w);
+    const int span = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N + align_elems) + 7) & ~7;
+    const int rows = 2 * fpr + cfg->diff_frames;
+    const mmb::SmemLayout L = mmb::smem_layout(N, w, cfg->num_bands, p->n_passes, p->n_pieces, p->w_floats, rows, span,
+                                               p->sample_bytes);
+    if (L.total <= (int)prop.sharedMemPerBlockOptin) {
+      p->warps = w; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
+      break;
+    }
+  }
+  if (p->warps == 0) {
     mmb_plan_destroy(p);
     return fail(MMB_E_UNSUPPORTED, "configuration needs more shared memory than one SM has (hop_size or filterbank too large)");
   }
-  e = mmb::frontend_max_ctas_per_sm(N, p->sample_bytes, p->smem_bytes, &p->ctas_per_sm);
-  if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "occupancy query"); }
-  if (p->ctas_per_sm < 1) { mmb_plan_destroy(p); return fail(MMB_E_UNSUPPORTED, "kernel does not fit on an SM"); }
+  e = mmb::frontend_set_smem(N, p->sample_bytes, (int)prop.sharedMemPerBlockOptin);
+  if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)"); }
+  const int fpr = mmb::frames_per_round(N, p->warps);
   p->chunk_frames = cfg->chunk_frames > 0 ? cfg->chunk_frames : 32 * fpr - cfg->diff_frames;
   *out = p;
   return MMB_OK;
@@ -163,8 +227,9 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
 extern "C" int mmb_plan_get_info(const mmb_plan* p, mmb_plan_info* info) {
   if (!p || !info) return fail(MMB_E_INVALID, "null argument");
   info->frame_size = p->cfg.frame_size; info->num_bins = p->cfg.frame_size / 2; info->num_bands = p->cfg.num_bands;
-  info->chunk_frames = p->chunk_frames; info->smem_bytes = p->smem_bytes; info->ctas_per_sm = p->ctas_per_sm;
-  info->num_sms = p->num_sms; info->frames_per_round = mmb::frames_per_round(p->cfg.frame_size);
+  info->chunk_frames = p->chunk_frames; info->smem_bytes = p->smem_bytes; info->ctas_per_sm = 1;
+  info->num_sms = p->num_sms; info->frames_per_round = mmb::frames_per_round(p->cfg.frame_size, p->warps);
+  info->warps = p->warps;
   return MMB_OK;
 }
 
@@ -209,6 +274,7 @@ extern "C" int mmb_layout_create(const mmb_plan* p, const mmb_track* units, int3
   build_prefix(p, units, n, prefix, &l->total_rows);
   l->n = n;
   l->total_chunks = prefix[n];
+  for (int32_t i = 0; i < n; ++i) l->pcm_extent = std::max(l->pcm_extent, units[i].pcm_offset + units[i].pcm_len);
   std::vector<Track> t(n);
   std::memcpy(t.data(), units, sizeof(Track) * n);
   cudaError_t e;
@@ -233,7 +299,7 @@ static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
 }
 
 static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_prefix, int32_t n, int32_t chunks,
-                  const void* pcm_dev, const mmb_outputs* o, cudaStream_t stream) {
+                  const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream) {
   FrontendParams fp;
   std::memset(&fp, 0, sizeof(fp));
   fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunk_prefix = d_prefix; fp.n_tracks = n; fp.total_chunks = chunks;
@@ -241,8 +307,11 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.win = p->d_win; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
   const bool band_out = o->filt || o->log || o->diff || o->odf;
   fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only stft/spec are wanted
-  fp.nnz = band_out ? p->nnz : 0;
-  fp.band_start = p->d_bstart; fp.band_len = p->d_blen; fp.band_woff = p->d_bwoff; fp.weights = p->d_w;
+  fp.n_passes = p->n_passes; fp.n_pieces = p->n_pieces; fp.w_floats = p->w_floats;
+  fp.fb_pass = p->d_pass; fp.fb_w = p->d_fbw; fp.fb_start = p->d_fbstart; fp.fb_pid = p->d_fbpid;
+  fp.band_pstart = p->d_pstart;
+  fp.pcm_extent = pcm_extent; fp.bulk_allowed = ((uintptr_t)pcm_dev % 16) == 0;
+  fp.warps = p->warps; fp.ring_rows = p->ring_rows;
   fp.mul = p->cfg.mul; fp.add = p->cfg.add; fp.log_mode = p->cfg.log_mode;
   fp.diff_frames = p->cfg.diff_frames; fp.max_bins = p->cfg.diff_max_bins; fp.positive = p->cfg.positive_diffs;
   fp.circular_shift = p->cfg.circular_shift;
@@ -250,12 +319,10 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.out_stft = (float2*)o->stft; fp.ld_stft = o->ld_stft; fp.out_spec = o->spec; fp.ld_spec = o->ld_spec;
   fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
   fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;
-  // the shared-memory layout depends on n_bands/nnz actually used
-  const mmb::SmemLayout L = mmb::smem_layout(p->cfg.frame_size, fp.n_bands, fp.nnz, p->span_cap, p->sample_bytes);
-  int grid = p->ctas_per_sm * p->num_sms;
+  int grid = p->num_sms;                              // one persistent CTA per SM
   if (grid > chunks) grid = chunks;
   if (grid < 1) return MMB_OK;
-  cudaError_t e = mmb::launch_frontend(p->cfg.frame_size, p->sample_bytes, fp, grid, L.total, stream);
+  cudaError_t e = mmb::launch_frontend(p->cfg.frame_size, p->sample_bytes, fp, grid, p->smem_bytes, stream);
   if (e != cudaSuccess) return cuda_fail(e, "frontend kernel launch");
   return MMB_OK;
 }
@@ -267,7 +334,7 @@ extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_d
   int rc = check_outputs(p, outs);
   if (rc) return rc;
   CU(cudaSetDevice(p->cfg.device));
-  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, pcm_dev, outs, (cudaStream_t)stream);
+  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, pcm_dev, l->pcm_extent, outs, (cudaStream_t)stream);
   if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
   return rc;
 }
@@ -396,7 +463,8 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
       // pageable tab/prefix vectors are reused by the next group: the async copies above are staged
       // synchronously by the runtime for pageable memory, so this is safe.
       if (prefix.back() > 0) {
-        status = launch(p, S.d_tracks, S.d_prefix, (int32_t)tab.size(), prefix.back(), S.d_pcm, &od, S.stream);
+        status = launch(p, S.d_tracks, S.d_prefix, (int32_t)tab.size(), prefix.back(), S.d_pcm, pcm1 - pcm0, &od,
+                        S.stream);
         if (status) goto done;
         ++n_launch;
         for (int k = 0; k < 6; ++k) {

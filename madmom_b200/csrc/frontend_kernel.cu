@@ -9,10 +9,14 @@
 //
 // Work decomposition
 //   unit   = track (or frame range of a long signal), split into chunks of `chunk_frames` output frames
-//   CTA    = persistent, strides over chunks; a chunk is walked in rounds of FPR consecutive frames
-//   warp   = one frame per round (two for N=1024): register-resident 32x32 FFT (fft_core.cuh)
-//   round  = stage PCM span -> [A] per-warp FFT + magnitudes -> [B] CTA-wide filterbank + log into a
-//            32-row ring -> [C] per-warp max-filter / difference / flux and coalesced row stores
+//   CTA    = persistent (one per SM), strides over chunks; a chunk is walked in rounds of FPR consecutive frames
+//   round  = the PCM span of the round is staged into one of two shared-memory buffers by ONE cp.async.bulk
+//            (TMA bulk copy, mbarrier completion) issued a full round ahead; spans that touch the edge of a
+//            signal are filled by the threads with zero padding instead
+//   warp   = owns one frame per round (two for N = 1024) end to end: register-resident 32x32 FFT
+//            (fft_core.cuh) -> magnitudes in its scratch -> its own filterbank pass (FbPass schedule) -> log ->
+//            one row of the CTA's log-spectrogram ring
+//   barrier= ONE __syncthreads per round, between "rows written" and "lagged difference read"
 // A chunk recomputes its `diff_frames` lead-in frames instead of exchanging them with its neighbour.
 #include "frame_fft.cuh"
 #include "frontend_params.h"
@@ -24,51 +28,47 @@ __device__ __forceinline__ long long frame_start_sample(long long g, double hop,
   return __double2ll_rz((double)g * hop) - (long long)(N / 2) - (long long)origin;
 }
 
-__device__ __forceinline__ float fast_log10(float y) { return __log2f(y) * 0.30102999566398119521f; }
+// ---------------------------------------------------------------------------------------------- mbarrier / TMA
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (UBLKCP); dst, src 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ---------------------------------------------------------------------------------------------- round cursor
+// Thread 0 walks the CTA's rounds; `d` is filled for the round that follows (chunk, g0_prev, nfr_prev).
 template <int N, typename S>
-__global__ void __launch_bounds__(warps_per_cta(N) * 32, 1) frontend_kernel(const FrontendParams p) {
-  constexpr int kWarps = warps_per_cta(N);
-  constexpr int kThreads = kWarps * 32;
-  extern __shared__ __align__(16) unsigned char smem[];
-  constexpr int FPR = frames_per_round(N);
-  constexpr int K = N / 2;
-  const SmemLayout L = smem_layout(N, p.n_bands, p.nnz, p.span_cap, (int)sizeof(S));
-  float* s_win = reinterpret_cast<float*>(smem + L.win);
-  float2* s_tw1 = reinterpret_cast<float2*>(smem + L.tw1);
-  float2* s_tw2k = reinterpret_cast<float2*>(smem + L.tw2k);
-  float2* s_tw4k = reinterpret_cast<float2*>(smem + L.tw4k);
-  int* s_bstart = reinterpret_cast<int*>(smem + L.fb_meta);
-  int* s_blen = s_bstart + p.n_bands;
-  int* s_bwoff = s_blen + p.n_bands;
-  float* s_w = reinterpret_cast<float*>(smem + L.fb_w);
-  float* s_ring = reinterpret_cast<float*>(smem + L.ring);
-  S* s_pcm = reinterpret_cast<S*>(smem + L.pcm);
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  unsigned char* my_scratch = smem + L.scratch + warp * warp_scratch_bytes(N);
-  float2* ex = reinterpret_cast<float2*>(my_scratch);
-  float* my_mag = (N == 4096) ? reinterpret_cast<float*>(my_scratch + 8448) : reinterpret_cast<float*>(my_scratch);
-
-  // ---- plan constants -> shared memory (once per persistent CTA)
-  for (int i = tid; i < N; i += kThreads) s_win[i] = p.win[i];
-  for (int i = tid; i < 1024; i += kThreads) s_tw1[i] = p.tw1[i];
-  if (N != 1024) for (int i = tid; i < 1024; i += kThreads) s_tw2k[i] = p.tw2k[i];
-  if (N == 4096) for (int i = tid; i < 512; i += kThreads) s_tw4k[i] = p.tw4k[i];
-  for (int i = tid; i < p.n_bands; i += kThreads) {
-    s_bstart[i] = p.band_start[i]; s_blen[i] = p.band_len[i]; s_bwoff[i] = p.band_woff[i];
+__device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, int fpr) {
+  const int lead = ((p.out_diff != nullptr) || (p.out_odf != nullptr)) ? p.diff_frames : 0;
+  long long g0;
+  bool new_chunk = first;
+  int chunk = first ? (int)blockIdx.x : d.chunk;
+  if (!first) {
+    g0 = d.g0 + d.nfr;
+    if (g0 >= d.gb) { chunk += (int)gridDim.x; new_chunk = true; }
   }
-  for (int i = tid; i < p.nnz; i += kThreads) s_w[i] = p.weights[i];
-  __syncthreads();
-
-  const S* __restrict__ pcm = reinterpret_cast<const S*>(p.pcm);
-  const int nb = p.n_bands;
-  const bool want_diff = (p.out_diff != nullptr) || (p.out_odf != nullptr);
-  const int lead = want_diff ? p.diff_frames : 0;
-  const float sgn_odd = p.circular_shift ? -1.0f : 1.0f;
-
-  for (int chunk = blockIdx.x; chunk < p.total_chunks; chunk += gridDim.x) {
-    // ---- locate the unit this chunk belongs to (binary search over the prefix table)
+  if (new_chunk) {
+    if (chunk >= p.total_chunks) { d.nfr = 0; return; }
     int lo = 0, hi = p.n_tracks;
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
@@ -77,163 +77,326 @@ __global__ void __launch_bounds__(warps_per_cta(N) * 32, 1) frontend_kernel(cons
     const Track tr = p.tracks[lo];
     const long long a_loc = (long long)(chunk - p.chunk_prefix[lo]) * p.chunk_frames;
     const long long b_loc = min(a_loc + (long long)p.chunk_frames, (long long)tr.frame_count);
-    const long long ga = tr.frame_first + a_loc, gb = tr.frame_first + b_loc;   // global frame range
-    const long long g_begin = max(ga - (long long)lead, 0LL);
+    d.chunk = chunk; d.unit = lo;
+    d.ga = tr.frame_first + a_loc; d.gb = tr.frame_first + b_loc;
+    d.row0 = tr.out_row - tr.frame_first;
+    d.pcm_offset = tr.pcm_offset; d.pcm_len = tr.pcm_len;
+    d.sample_base = tr.sample_base;
+    g0 = max(d.ga - (long long)lead, 0LL);
+  }
+  d.g0 = g0;
+  d.nfr = (int)min((long long)fpr, d.gb - g0);
+  d.s_begin = frame_start_sample(g0, p.hop, N, p.origin);
+  const long long s_end = frame_start_sample(g0 + d.nfr - 1, p.hop, N, p.origin) + N;
+  d.span = (int)(s_end - d.s_begin);
+  d.l0 = d.s_begin - d.sample_base;
+  d.slot0 = (int)(g0 % (long long)p.ring_rows);
+  // bulk staging: every staged sample is a real sample of the unit and the 16-byte aligned hull stays inside
+  // the PCM buffer
+  constexpr int A = 16 / (int)sizeof(S);
+  const long long abs0 = d.pcm_offset + d.l0;
+  const long long e0 = abs0 & ~(long long)(A - 1);
+  const long long e1 = (abs0 + d.span + A - 1) & ~(long long)(A - 1);
+  d.bulk = p.bulk_allowed && d.l0 >= 0 && d.l0 + d.span <= d.pcm_len && e1 <= p.pcm_extent &&
+           (e1 - e0) <= (long long)p.span_cap;
+  d.shift = d.bulk ? (int)(abs0 - e0) : 0;
+}
 
-    for (long long g0 = g_begin; g0 < gb; g0 += FPR) {
-      const int nfr = (int)min((long long)FPR, gb - g0);
-      // ---- stage the PCM span of this round (zero outside the unit's local samples)
-      const long long s_begin = frame_start_sample(g0, p.hop, N, p.origin);
-      const long long s_end = frame_start_sample(g0 + nfr - 1, p.hop, N, p.origin) + N;
-      const int span = (int)(s_end - s_begin);
-      {
-        const long long l0 = s_begin - tr.sample_base;       // local index of span[0]
-        const S* src = pcm + tr.pcm_offset;
-        for (int i = tid; i < span; i += kThreads) {
-          const long long li = l0 + i;
-          S v = (S)0;
-          if (li >= 0 && li < tr.pcm_len) v = src[li];
-          s_pcm[i] = v;
+template <typename S>
+__device__ __forceinline__ void issue_bulk(const FrontendParams& p, const RoundDesc& d, S* buf, uint64_t* bar) {
+  constexpr int A = 16 / (int)sizeof(S);
+  const long long abs0 = d.pcm_offset + d.l0;
+  const long long e0 = abs0 & ~(long long)(A - 1);
+  const long long e1 = (abs0 + d.span + A - 1) & ~(long long)(A - 1);
+  const uint32_t bytes = (uint32_t)((e1 - e0) * (long long)sizeof(S));
+  fence_proxy_async();                            // earlier generic-proxy accesses of buf are ordered before the copy
+  mbar_expect_tx(bar, bytes);
+  bulk_g2s(buf, reinterpret_cast<const S*>(p.pcm) + e0, bytes, bar);
+}
+
+// ---------------------------------------------------------------------------------------------- per-warp stages
+// Filterbank of one frame (two for N = 1024) owned by this warp: FbPass schedule over the magnitudes in the
+// warp's scratch, then the per-band sum of pieces, log scaling and the ring row.  `mag1` is the second frame of a
+// 1024-point pair or null.
+template <int NF>
+__device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lane, const float* __restrict__ mag0,
+                                                const float* __restrict__ mag1, float* part,
+                                                const FbPass* __restrict__ s_pass, const float* __restrict__ s_w,
+                                                const int* __restrict__ s_start, const int* __restrict__ s_pid) {
+  const int np1 = p.n_pieces + 1;
+  for (int ps = 0; ps < p.n_passes; ++ps) {
+    const FbPass fp = s_pass[ps];
+    const int st = s_start[ps * 32 + lane];
+    const float* w = s_w + fp.woff + lane;
+    const float* m0 = mag0 + st;
+    const float* m1 = mag1 + st;
+    float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll 4
+    for (int i = 0; i < fp.iters; ++i) {
+      const float wi = w[i * 32];
+      a0 = fmaf(m0[i], wi, a0);
+      if (NF == 2) a1 = fmaf(m1[i], wi, a1);
+    }
+    const int pid = s_pid[ps * 32 + lane];
+    part[pid] = a0;
+    if (NF == 2) part[np1 + pid] = a1;
+  }
+  __syncwarp();
+}
+
+// rows of the ring / outputs for one frame g handled by this warp
+__device__ __forceinline__ void warp_band_epilogue(const FrontendParams& p, int lane, const float* part,
+                                                   const int* __restrict__ s_pstart, float* ring_row, long long row,
+                                                   bool emit) {
+  const int nb = p.n_bands;
+  for (int b = lane; b < nb; b += 32) {
+    const int q0 = s_pstart[b], q1 = s_pstart[b + 1];
+    float acc = 0.0f;
+    for (int q = q0; q < q1; ++q) acc += part[q];
+    if (emit && p.out_filt) p.out_filt[row * p.ld_filt + b] = acc;
+    ring_row[b] = p.log_mode != 0 ? log_scaled(acc, p.log_mode, p.mul, p.add) : acc;
+  }
+}
+
+// lagged difference of frame g against the ring row of frame g - d (phase C)
+__device__ __forceinline__ void warp_difference(const FrontendParams& p, int lane, const float* cur,
+                                                const float* prev, bool has_prev, long long row) {
+  const int nb = p.n_bands;
+  if (p.out_log) {
+    float* o = p.out_log + row * p.ld_log;
+    for (int b = lane; b < nb; b += 32) o[b] = cur[b];
+  }
+  if (p.out_diff == nullptr && p.out_odf == nullptr) return;
+  float sum = 0.0f;
+  const int m = p.max_bins, half = m / 2;
+  for (int b = lane; b < nb; b += 32) {
+    float dv = 0.0f;
+    if (has_prev) {
+      float ref;
+      if (m > 1) {                                       // scipy maximum_filter, mode='reflect'
+        ref = -INFINITY;
+        for (int j = 0; j < m; ++j) {
+          int q = b - half + j;
+          q = q < 0 ? -q - 1 : (q >= nb ? 2 * nb - q - 1 : q);
+          ref = fmaxf(ref, prev[q]);
         }
+      } else {
+        ref = prev[b];
       }
-      __syncthreads();
-
-      // ================= phase A: per-warp FFT -> magnitudes in warp scratch (+ optional stft/spec rows)
-      {
-        float2 v[32];
-        if (N == 1024) {
-          const int fa = 2 * warp, fb = 2 * warp + 1;
-          if (fa < nfr) {
-            const long long gA = g0 + fa, gB = g0 + fb;
-            const bool haveB = fb < nfr;
-            const S* xa = s_pcm + (int)(frame_start_sample(gA, p.hop, N, p.origin) - s_begin);
-            const S* xb = haveB ? s_pcm + (int)(frame_start_sample(gB, p.hop, N, p.origin) - s_begin) : nullptr;
-            load_frames_1024<S>(lane, v, xa, xb, s_win);
-            core_pass1(lane, v, ex, s_tw1);
-            __syncwarp();
-            core_pass2_load(lane, v, ex);
-            __syncwarp();
-            core_pass2_fft(v);
-            core_publish_upper(lane, v, ex, true);
-            __syncwarp();
-            BinSink oa, ob;
-            const long long rowA = tr.out_row + (gA - tr.frame_first), rowB = rowA + 1;
-            oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
-            oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
-            oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
-            ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
-            oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
-            ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
-            split_1024x2(lane, v, ex, oa, ob, haveB);
-          }
-        } else if (warp < nfr) {
-          const long long g = g0 + warp;
-          const S* x = s_pcm + (int)(frame_start_sample(g, p.hop, N, p.origin) - s_begin);
-          BinSink o;
-          const long long row = tr.out_row + (g - tr.frame_first);
-          o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
-          o.stft_row = (p.out_stft && g >= ga) ? p.out_stft + row * p.ld_stft : nullptr;
-          o.spec_row = (p.out_spec && g >= ga) ? p.out_spec + row * p.ld_spec : nullptr;
-          if (N == 2048) {
-            load_frame_2048<S>(lane, v, x, s_win);
-            core_pass1(lane, v, ex, s_tw1);
-            __syncwarp();
-            core_pass2_load(lane, v, ex);
-            __syncwarp();
-            core_pass2_fft(v);
-            core_publish_upper(lane, v, ex, true);
-            __syncwarp();
-            split_2048(lane, v, ex, s_tw2k, o);
-          } else {
-#pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
-              load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
-              core_pass1(lane, v, ex, s_tw1);
-              __syncwarp();
-              core_pass2_load(lane, v, ex);
-              __syncwarp();
-              core_pass2_fft(v);
-              core_publish_upper(lane, v, ex, c == 0);
-              __syncwarp();
-              split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
-              __syncwarp();
-            }
-          }
-        }
-      }
-      if (nb == 0) { __syncthreads(); continue; }
-      __syncthreads();
-
-      // ================= phase B: banded filterbank (FP32 FMA) + log into the ring
-      for (int item = tid; item < FPR * nb; item += kThreads) {
-        const int fi = item % FPR, b = item / FPR;
-        if (fi >= nfr) continue;
-        const float* mg = (N == 1024)
-            ? reinterpret_cast<const float*>(smem + L.scratch + (fi >> 1) * warp_scratch_bytes(N)) + (fi & 1) * 512
-            : reinterpret_cast<const float*>(smem + L.scratch + fi * warp_scratch_bytes(N) + (N == 4096 ? 8448 : 0));
-        const int st = s_bstart[b], ln = s_blen[b];
-        const float* w = s_w + s_bwoff[b];
-        float acc = 0.0f;
-        for (int i = 0; i < ln; ++i) acc = fmaf(mg[st + i], w[i], acc);
-        const long long g = g0 + fi;
-        if (p.out_filt && g >= ga) p.out_filt[(tr.out_row + (g - tr.frame_first)) * p.ld_filt + b] = acc;
-        const float y = p.log_mode != 0 ? log_scaled(acc, p.log_mode, p.mul, p.add) : acc;
-        s_ring[(int)(g & (kRing - 1)) * nb + b] = y;
-      }
-      __syncthreads();
-
-      // ================= phase C: max-filter + lagged difference + flux, coalesced row stores
-      for (int fi = warp; fi < nfr; fi += kWarps) {
-        const long long g = g0 + fi;
-        if (g < ga) continue;                                   // lead-in frame: ring only
-        const long long row = tr.out_row + (g - tr.frame_first);
-        const float* cur = s_ring + (int)(g & (kRing - 1)) * nb;
-        if (p.out_log) {
-          float* o = p.out_log + row * p.ld_log;
-          for (int b = lane; b < nb; b += 32) o[b] = cur[b];
-        }
-        if (want_diff) {
-          const bool has_prev = (g - p.diff_frames) >= 0;       // first d rows of a signal are zero
-          const float* prev = s_ring + (int)((g - p.diff_frames) & (kRing - 1)) * nb;
-          float sum = 0.0f;
-          const int m = p.max_bins, half = m / 2;
-          for (int b = lane; b < nb; b += 32) {
-            float dv = 0.0f;
-            if (has_prev) {
-              float ref;
-              if (m > 1) {                                       // scipy maximum_filter, mode='reflect'
-                ref = -INFINITY;
-                for (int j = 0; j < m; ++j) {
-                  int q = b - half + j;
-                  q = q < 0 ? -q - 1 : (q >= nb ? 2 * nb - q - 1 : q);
-                  ref = fmaxf(ref, prev[q]);
-                }
-              } else {
-                ref = prev[b];
-              }
-              dv = cur[b] - ref;
-              if (p.positive) dv = fmaxf(dv, 0.0f);
-            }
-            if (p.out_diff) p.out_diff[row * p.ld_diff + b] = dv;
-            sum += dv;
-          }
-          if (p.out_odf) {
+      dv = cur[b] - ref;
+      if (p.positive) dv = fmaxf(dv, 0.0f);
+    }
+    if (p.out_diff) p.out_diff[row * p.ld_diff + b] = dv;
+    sum += dv;
+  }
+  if (p.out_odf) {
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-            if (lane == 0) p.out_odf[row] = sum;
-          }
-        }
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) p.out_odf[row] = sum;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- the kernel
+template <int N, typename S>
+__global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const FrontendParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  constexpr int K = N / 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nthreads = blockDim.x, warps = nthreads >> 5;
+  const int FPR = frames_per_round(N, warps);
+  const SmemLayout L = smem_layout(N, warps, p.n_bands, p.n_passes, p.n_pieces, p.w_floats, p.ring_rows, p.span_cap,
+                                   (int)sizeof(S));
+  uint64_t* s_mbar = reinterpret_cast<uint64_t*>(smem + L.mbar);
+  RoundDesc* s_desc = reinterpret_cast<RoundDesc*>(smem + L.desc);
+  float* s_win = reinterpret_cast<float*>(smem + L.win);
+  float2* s_tw1 = reinterpret_cast<float2*>(smem + L.tw1);
+  float2* s_tw2k = reinterpret_cast<float2*>(smem + L.tw2k);
+  float2* s_tw4k = reinterpret_cast<float2*>(smem + L.tw4k);
+  FbPass* s_pass = reinterpret_cast<FbPass*>(smem + L.fb_pass);
+  float* s_w = reinterpret_cast<float*>(smem + L.fb_w);
+  int* s_start = reinterpret_cast<int*>(smem + L.fb_start);
+  int* s_pid = reinterpret_cast<int*>(smem + L.fb_pid);
+  int* s_pstart = reinterpret_cast<int*>(smem + L.band_pstart);
+  float* s_ring = reinterpret_cast<float*>(smem + L.ring);
+  const int pcm_stride = mmb_align16(p.span_cap * (int)sizeof(S));
+
+  unsigned char* my_scratch = smem + L.scratch + warp * warp_scratch_bytes(N);
+  float2* ex = reinterpret_cast<float2*>(my_scratch);
+  float* my_mag = (N == 4096) ? reinterpret_cast<float*>(my_scratch + 8448) : reinterpret_cast<float*>(my_scratch);
+  float* my_part = reinterpret_cast<float*>(smem + L.part + warp * L.part_stride);
+
+  // ---- plan constants -> shared memory (once per persistent CTA)
+  for (int i = tid; i < N; i += nthreads) s_win[i] = p.win[i];
+  for (int i = tid; i < 1024; i += nthreads) s_tw1[i] = p.tw1[i];
+  if (N == 2048) for (int i = tid; i < 512; i += nthreads) s_tw2k[i] = p.tw2k[i];
+  if (N == 4096) {
+    for (int i = tid; i < 1024; i += nthreads) s_tw2k[i] = p.tw2k[i];
+    for (int i = tid; i < 512; i += nthreads) s_tw4k[i] = p.tw4k[i];
+  }
+  const int nb = p.n_bands;
+  if (nb > 0) {
+    for (int i = tid; i < p.n_passes; i += nthreads) s_pass[i] = p.fb_pass[i];
+    for (int i = tid; i < p.w_floats; i += nthreads) s_w[i] = p.fb_w[i];
+    for (int i = tid; i < p.n_passes * 32; i += nthreads) { s_start[i] = p.fb_start[i]; s_pid[i] = p.fb_pid[i]; }
+    for (int i = tid; i <= nb; i += nthreads) s_pstart[i] = p.band_pstart[i];
+  }
+  if (tid == 0) {
+    mbar_init(&s_mbar[0], 1);
+    mbar_init(&s_mbar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    next_round<N, S>(p, s_desc[0], true, FPR);
+    if (s_desc[0].nfr > 0 && s_desc[0].bulk)
+      issue_bulk<S>(p, s_desc[0], reinterpret_cast<S*>(smem + L.pcm), &s_mbar[0]);
+  }
+  __syncthreads();
+
+  const bool want_diff = (p.out_diff != nullptr) || (p.out_odf != nullptr);
+  const float sgn_odd = p.circular_shift ? -1.0f : 1.0f;
+  const int R = p.ring_rows;
+  uint32_t phase0 = 0, phase1 = 0;          // parity of the next completion of each staging buffer's mbarrier
+  int prev_chunk = -1;
+
+  for (int r = 0;; ++r) {
+    const RoundDesc* D = &s_desc[r % 3];
+    const int nfr = D->nfr;
+    if (nfr == 0) break;
+    const int b = r & 1;
+    S* buf = reinterpret_cast<S*>(smem + L.pcm + b * pcm_stride);
+    // a new chunk maps its frames to unrelated ring slots: wait until the slowest warp has finished reading the
+    // previous chunk's rows (within a chunk the ring is large enough for one round of skew)
+    if (D->chunk != prev_chunk) {
+      if (r > 0) __syncthreads();
+      prev_chunk = D->chunk;
+    }
+    // ---- thread 0: describe the following round and start its bulk copy into the other buffer (its last
+    //      readers finished before the barrier of the previous round)
+    if (tid == 0) {
+      RoundDesc* Dn = &s_desc[(r + 1) % 3];
+      *Dn = *D;
+      next_round<N, S>(p, *Dn, false, FPR);
+      if (Dn->nfr > 0 && Dn->bulk)
+        issue_bulk<S>(p, *Dn, reinterpret_cast<S*>(smem + L.pcm + (b ^ 1) * pcm_stride), &s_mbar[b ^ 1]);
+    }
+    // ---- this round's PCM span
+    if (D->bulk) {
+      mbar_wait(&s_mbar[b], b ? phase1 : phase0);
+      if (b) phase1 ^= 1; else phase0 ^= 1;
+    } else {
+      const long long l0 = D->l0, plen = D->pcm_len;
+      const S* src = reinterpret_cast<const S*>(p.pcm) + D->pcm_offset;
+      const int span = D->span;
+      for (int i = tid; i < span; i += nthreads) {
+        const long long li = l0 + i;
+        S v = (S)0;
+        if (li >= 0 && li < plen) v = src[li];
+        buf[i] = v;
       }
       __syncthreads();
+    }
+    const long long g0 = D->g0, ga = D->ga, row0 = D->row0, s_begin = D->s_begin;
+    const S* span0 = buf + D->shift;
+    const int slot0 = D->slot0;
+
+    // ================= phase A+B: this warp's frame(s): FFT -> magnitudes -> filterbank -> ring row
+    {
+      float2 v[32];
+      if (N == 1024) {
+        const int fa = 2 * warp, fb = 2 * warp + 1;
+        if (fa < nfr) {
+          const long long gA = g0 + fa, gB = g0 + fb;
+          const bool haveB = fb < nfr;
+          const S* xa = span0 + (int)(frame_start_sample(gA, p.hop, N, p.origin) - s_begin);
+          const S* xb = haveB ? span0 + (int)(frame_start_sample(gB, p.hop, N, p.origin) - s_begin) : nullptr;
+          load_frames_1024<S>(lane, v, xa, xb, s_win);
+          core_pass1(lane, v, ex, s_tw1);
+          __syncwarp();
+          core_pass2_load(lane, v, ex);
+          __syncwarp();
+          core_pass2_fft(v);
+          core_publish_upper(lane, v, ex, true);
+          __syncwarp();
+          BinSink oa, ob;
+          const long long rowA = row0 + gA, rowB = rowA + 1;
+          oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
+          oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
+          oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
+          ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
+          oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
+          ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
+          split_1024x2(lane, v, ex, oa, ob, haveB);
+          if (nb > 0) {
+            __syncwarp();
+            if (!haveB) for (int i = lane; i < 512; i += 32) my_mag[512 + i] = 0.0f;
+            __syncwarp();
+            warp_filterbank<2>(p, lane, my_mag, my_mag + 512, my_part, s_pass, s_w, s_start, s_pid);
+            int sa = slot0 + fa; if (sa >= R) sa -= R;
+            warp_band_epilogue(p, lane, my_part, s_pstart, s_ring + sa * nb, rowA, gA >= ga);
+            if (haveB) {
+              int sb = sa + 1; if (sb >= R) sb -= R;
+              warp_band_epilogue(p, lane, my_part + p.n_pieces + 1, s_pstart, s_ring + sb * nb, rowB, gB >= ga);
+            }
+          }
+        }
+      } else if (warp < nfr) {
+        const long long g = g0 + warp;
+        const S* x = span0 + (int)(frame_start_sample(g, p.hop, N, p.origin) - s_begin);
+        BinSink o;
+        const long long row = row0 + g;
+        o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
+        o.stft_row = (p.out_stft && g >= ga) ? p.out_stft + row * p.ld_stft : nullptr;
+        o.spec_row = (p.out_spec && g >= ga) ? p.out_spec + row * p.ld_spec : nullptr;
+        if (N == 2048) {
+          load_frame_2048<S>(lane, v, x, s_win);
+          core_pass1(lane, v, ex, s_tw1);
+          __syncwarp();
+          core_pass2_load(lane, v, ex);
+          __syncwarp();
+          core_pass2_fft(v);
+          core_publish_upper(lane, v, ex, true);
+          __syncwarp();
+          split_2048(lane, v, ex, s_tw2k, o);
+        } else {
+#pragma unroll 1
+          for (int c = 0; c < 2; ++c) {
+            load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
+            core_pass1(lane, v, ex, s_tw1);
+            __syncwarp();
+            core_pass2_load(lane, v, ex);
+            __syncwarp();
+            core_pass2_fft(v);
+            core_publish_upper(lane, v, ex, c == 0);
+            __syncwarp();
+            split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
+            __syncwarp();
+          }
+        }
+        if (nb > 0) {
+          __syncwarp();
+          warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
+          int sl = slot0 + warp; if (sl >= R) sl -= R;
+          warp_band_epilogue(p, lane, my_part, s_pstart, s_ring + sl * nb, row, g >= ga);
+        }
+      }
+    }
+    __syncthreads();          // ring rows of the round are complete; staging buffer b is free again
+    if (nb == 0) continue;
+
+    // ================= phase C: max-filter + lagged difference + flux, coalesced row stores
+    for (int fi = warp; fi < nfr; fi += warps) {
+      const long long g = g0 + fi;
+      if (g < ga) continue;                                   // lead-in frame: ring only
+      int sc = slot0 + fi; while (sc >= R) sc -= R;
+      int sp = sc - p.diff_frames; if (sp < 0) sp += R;
+      const bool has_prev = want_diff && (g - p.diff_frames) >= 0;       // first d rows of a signal are zero
+      warp_difference(p, lane, s_ring + sc * nb, s_ring + sp * nb, has_prev, row0 + g);
     }
   }
 }
 
+// ---------------------------------------------------------------------------------------------- host launchers
 template <int N, typename S>
 static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-  if (e != cudaSuccess) return e;
-  frontend_kernel<N, S><<<grid, warps_per_cta(N) * 32, smem_bytes, stream>>>(p);
+  frontend_kernel<N, S><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
   return cudaGetLastError();
 }
 
@@ -252,21 +415,20 @@ cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, in
 }
 
 template <int N, typename S>
-static cudaError_t occ_one(int smem_bytes, int* out) {
-  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-  if (e != cudaSuccess) return e;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, frontend_kernel<N, S>, warps_per_cta(N) * 32, smem_bytes);
+static cudaError_t set_one(int smem_bytes) {
+  return cudaFuncSetAttribute(frontend_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
 }
 
-cudaError_t frontend_max_ctas_per_sm(int N, int sample_bytes, int smem_bytes, int* out) {
+// opt the kernel variant in to `smem_bytes` of dynamic shared memory (once per plan)
+cudaError_t frontend_set_smem(int N, int sample_bytes, int smem_bytes) {
   if (sample_bytes == 2) {
-    if (N == 1024) return occ_one<1024, int16_t>(smem_bytes, out);
-    if (N == 2048) return occ_one<2048, int16_t>(smem_bytes, out);
-    if (N == 4096) return occ_one<4096, int16_t>(smem_bytes, out);
+    if (N == 1024) return set_one<1024, int16_t>(smem_bytes);
+    if (N == 2048) return set_one<2048, int16_t>(smem_bytes);
+    if (N == 4096) return set_one<4096, int16_t>(smem_bytes);
   } else if (sample_bytes == 4) {
-    if (N == 1024) return occ_one<1024, float>(smem_bytes, out);
-    if (N == 2048) return occ_one<2048, float>(smem_bytes, out);
-    if (N == 4096) return occ_one<4096, float>(smem_bytes, out);
+    if (N == 1024) return set_one<1024, float>(smem_bytes);
+    if (N == 2048) return set_one<2048, float>(smem_bytes);
+    if (N == 4096) return set_one<4096, float>(smem_bytes);
   }
   return cudaErrorInvalidValue;
 }

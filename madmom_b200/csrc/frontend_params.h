@@ -16,8 +16,21 @@ struct Track {
   int64_t out_row;       // first output row of this unit
 };
 
+// Per-warp filterbank schedule (built on the host, capi.cu): every band is cut into pieces of at most
+// kPieceBins bins; pieces are sorted by length and dealt to the 32 lanes pass by pass.  In pass p lane l
+// accumulates   sum_i mag[start[p][l] + i] * w[p][i][l],  i < iters[p]   (weights zero-padded to iters[p]),
+// stores the partial sum at part[pid[p][l]], and a second step adds the pieces of each band in order.
+struct FbPass {
+  int32_t iters;   // loop length of this pass (length of its longest piece)
+  int32_t woff;    // offset (floats) of w[p][0][0] inside the weight table
+};
+constexpr int kPieceBins = 16;
+constexpr int kMaxPasses = 16;
+
 struct FrontendParams {
   const void* pcm;               // int16 or float32 samples
+  int64_t pcm_extent;            // elements of the PCM buffer that may be read (max over units of offset + len)
+  int32_t bulk_allowed;          // PCM base is 16-byte aligned: rounds may be staged with cp.async.bulk
   const Track* tracks;
   const int32_t* chunk_prefix;   // [n_tracks + 1] prefix sum of chunks per track
   int32_t n_tracks;
@@ -25,18 +38,20 @@ struct FrontendParams {
   int32_t chunk_frames;          // output frames per chunk
   double hop;                    // frame i starts at (int64)(i * hop) - N/2 - origin   (signal.py:917-919)
   int32_t origin;
-  int32_t span_cap;              // capacity (samples) of the staged PCM span in shared memory
+  int32_t span_cap;              // capacity (samples) of one staged PCM span in shared memory
+  int32_t warps;                 // warps per CTA (blockDim.x / 32)
   // plan constants (device)
   const float* win;              // N floats, fft_window * 0.5
   const float2* tw1;             // 1024: W1024^(l*k1) at [k1*32 + l]
-  const float2* tw2k;            // 1024: W2048^k
+  const float2* tw2k;            // 1024: W2048^k (N = 2048 uses the first 512)
   const float2* tw4k;            // 512 : W4096^(2j+1)
   int32_t n_bands;               // 0 -> no filterbank stage
-  int32_t nnz;
-  const int32_t* band_start;
-  const int32_t* band_len;
-  const int32_t* band_woff;
-  const float* weights;
+  int32_t n_passes, n_pieces, w_floats;
+  const FbPass* fb_pass;         // [n_passes]
+  const float* fb_w;             // [w_floats]
+  const int32_t* fb_start;       // [n_passes * 32]
+  const int32_t* fb_pid;         // [n_passes * 32] piece id, n_pieces for idle lanes
+  const int32_t* band_pstart;    // [n_bands + 1] pieces of band b are part[pstart[b] .. pstart[b+1])
   float mul, add;
   int32_t log_mode;              // 0 none, 1 log10, 2 mul/add only, 3 ln, 4 log2
   int32_t diff_frames;           // d >= 1 when a difference is requested
@@ -44,6 +59,7 @@ struct FrontendParams {
   int32_t positive;
   int32_t circular_shift;
   int32_t spec_log_mode;         // log mode applied to the spec output (plans without a filterbank)
+  int32_t ring_rows;             // rows of the log-spectrogram ring: 2 * frames_per_round + diff_frames
   // outputs (device, row-major, leading dimensions in elements; null -> not produced)
   float2* out_stft; int64_t ld_stft;
   float* out_spec;  int64_t ld_spec;
@@ -53,40 +69,64 @@ struct FrontendParams {
   float* out_odf;
 };
 
-// warps per CTA: one CTA per SM; 16 warps (4 per scheduler) where the per-warp scratch allows it
-__host__ __device__ constexpr int warps_per_cta(int N) { return N == 2048 ? 16 : 8; }
-constexpr int kRing = 32;          // rows of the log-spectrogram ring (>= frames per round + max diff_frames)
+constexpr int kMaxWarps = 16;
 constexpr int kMaxDiffFrames = 16;
 
-// frames one CTA round produces
-__host__ __device__ constexpr int frames_per_round(int N) { return N == 1024 ? 2 * warps_per_cta(N) : warps_per_cta(N); }
+// frames one CTA round produces with `warps` warps
+__host__ __device__ constexpr int frames_per_round(int N, int warps) { return N == 1024 ? 2 * warps : warps; }
 // per-warp scratch (bytes): exchange tile (+ magnitudes aliased in its lower 4 KB; separate 8 KB for 4096)
 __host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? 8448 + 8192 : 8448) + 16; }
 
+// one descriptor per round, written by thread 0, read by everybody (3 slots, see frontend_kernel.cu)
+struct RoundDesc {
+  long long g0;          // first (global) frame of the round
+  long long ga;          // first output frame of the chunk (frames below are lead-in)
+  long long row0;        // output row of global frame g is row0 + g
+  long long s_begin;     // global sample index of the first staged sample
+  long long l0;          // local sample index of the first staged sample
+  long long pcm_offset, pcm_len, sample_base;
+  int nfr;               // frames in this round (0: no more work)
+  int span;              // staged samples
+  int bulk;              // staged by cp.async.bulk (else by the threads, with zero fill)
+  int shift;             // elements between the start of the staging buffer and sample s_begin
+  int slot0;             // ring slot of frame g0
+  int chunk, unit, pad;
+  long long gb;          // end of the chunk's output range
+};
+
 struct SmemLayout {
-  int win, tw1, tw2k, tw4k, fb_meta, fb_w, ring, scratch, pcm, total;
+  int mbar, desc, win, tw1, tw2k, tw4k, fb_pass, fb_w, fb_start, fb_pid, band_pstart, ring, scratch, part, pcm, total;
+  int part_stride;       // bytes of partial sums per warp
 };
 
 __host__ __device__ inline int mmb_align16(int x) { return (x + 15) & ~15; }
 
-__host__ __device__ inline SmemLayout smem_layout(int N, int n_bands, int nnz, int span_cap, int sample_bytes) {
+__host__ __device__ inline SmemLayout smem_layout(int N, int warps, int n_bands, int n_passes, int n_pieces,
+                                                  int w_floats, int ring_rows, int span_cap, int sample_bytes) {
   SmemLayout L;
   int o = 0;
-  L.win = o;     o += mmb_align16(N * 4);
-  L.tw1 = o;     o += 1024 * 8;
-  L.tw2k = o;    o += (N == 1024 ? 0 : 1024 * 8);
-  L.tw4k = o;    o += (N == 4096 ? 512 * 8 : 0);
-  L.fb_meta = o; o += mmb_align16(n_bands * 3 * 4);
-  L.fb_w = o;    o += mmb_align16(nnz * 4);
-  L.ring = o;    o += mmb_align16(n_bands > 0 ? kRing * n_bands * 4 : 0);
-  L.scratch = o; o += warps_per_cta(N) * warp_scratch_bytes(N);
-  L.pcm = o;     o += mmb_align16(span_cap * sample_bytes);
+  L.mbar = o;        o += 16;
+  L.desc = o;        o += mmb_align16(3 * (int)sizeof(RoundDesc));
+  L.win = o;         o += mmb_align16(N * 4);
+  L.tw1 = o;         o += 1024 * 8;
+  L.tw2k = o;        o += (N == 1024 ? 0 : (N == 2048 ? 512 * 8 : 1024 * 8));
+  L.tw4k = o;        o += (N == 4096 ? 512 * 8 : 0);
+  L.fb_pass = o;     o += mmb_align16(n_passes * (int)sizeof(FbPass));
+  L.fb_w = o;        o += mmb_align16(w_floats * 4);
+  L.fb_start = o;    o += mmb_align16(n_passes * 32 * 4);
+  L.fb_pid = o;      o += mmb_align16(n_passes * 32 * 4);
+  L.band_pstart = o; o += mmb_align16(n_bands > 0 ? (n_bands + 1) * 4 : 0);
+  L.ring = o;        o += mmb_align16(n_bands > 0 ? ring_rows * n_bands * 4 : 0);
+  L.scratch = o;     o += warps * warp_scratch_bytes(N);
+  L.part_stride = mmb_align16((n_pieces + 1) * 4 * (N == 1024 ? 2 : 1));
+  L.part = o;        o += n_bands > 0 ? warps * L.part_stride : 0;
+  L.pcm = o;         o += 2 * mmb_align16(span_cap * sample_bytes);
   L.total = o;
   return L;
 }
 
 cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, int grid, int smem_bytes,
                             cudaStream_t stream);
-cudaError_t frontend_max_ctas_per_sm(int N, int sample_bytes, int smem_bytes, int* out);
+cudaError_t frontend_set_smem(int N, int sample_bytes, int smem_bytes);
 
 }  // namespace mmb

@@ -35,12 +35,12 @@ struct mmb_plan {
   int warps = 0;
   int ring_rows = 0;
   int chunk_frames = 0;
-  int n_passes = 0, n_pieces = 0, w_floats = 0;
+  int n_passes = 0, max_q = 0, b_pad = 0, w_floats = 0, fb_iters = 0;
   float* d_win = nullptr;
   float2 *d_tw1 = nullptr, *d_tw2k = nullptr, *d_tw4k = nullptr;
   mmb::FbPass* d_pass = nullptr;
   float* d_fbw = nullptr;
-  int32_t *d_fbstart = nullptr, *d_fbpid = nullptr, *d_pstart = nullptr;
+  int32_t *d_fbstart = nullptr, *d_fbpid = nullptr;
 };
 
 struct mmb_layout {
@@ -77,57 +77,104 @@ static cudaError_t upload(T** dst, const std::vector<T>& src) {
 extern "C" int mmb_plan_destroy(mmb_plan* p) {
   if (!p) return MMB_OK;
   cudaFree(p->d_win); cudaFree(p->d_tw1); cudaFree(p->d_tw2k); cudaFree(p->d_tw4k);
-  cudaFree(p->d_pass); cudaFree(p->d_fbw); cudaFree(p->d_fbstart); cudaFree(p->d_fbpid); cudaFree(p->d_pstart);
+  cudaFree(p->d_pass); cudaFree(p->d_fbw); cudaFree(p->d_fbstart); cudaFree(p->d_fbpid);
   delete p;
   return MMB_OK;
 }
 
-// Per-warp filterbank schedule (frontend_params.h: FbPass).  Bands are cut into pieces of at most kPieceBins
-// bins, pieces are sorted by length (longest first) and dealt to the 32 lanes pass by pass; the weights of a pass
-// are stored [iteration][lane] and zero-padded to the pass's longest piece.
+// Per-warp filterbank schedule (frontend_params.h: FbPass).  Every band is cut into pieces of at most P bins.
+// A pass gives each of the 32 lanes at most one piece, chosen so that the lanes' first bins are distinct modulo
+// 32: lane l reads mag[start_l + i] in iteration i, so a pass is free of shared-memory bank conflicts by
+// construction.  A piece may be shifted down by `lead` bins (zero weights in front) to reach a free bank.  The
+// longest remaining piece sets the pass length; weights are stored [iteration][lane], zero padded.
+// The partial sum of piece q of band b is stored at part[q * b_pad + b]; the epilogue adds q = 0 .. max_q-1.
 namespace {
 struct FbSchedule {
   std::vector<mmb::FbPass> pass;
   std::vector<float> w;
-  std::vector<int32_t> start, pid, pstart;
-  int n_pieces = 0;
+  std::vector<int32_t> start, pid;
+  int max_q = 0, b_pad = 0, iters = 0;
 };
-struct Piece { int start, len, id; const float* w; };
+struct Piece { int start, len, band, q; const float* w; };
 
-void build_schedule(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, FbSchedule& s) {
+void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, int P, FbSchedule& s) {
   const int B = cfg->num_bands;
-  std::vector<Piece> pieces;
-  s.pstart.assign(B + 1, 0);
+  s = FbSchedule();
+  s.b_pad = (B + 31) & ~31;
+  std::vector<Piece> rem;
   for (int b = 0; b < B; ++b) {
     const int len = cfg->band_len[b];
-    const int n = len > 0 ? (len + mmb::kPieceBins - 1) / mmb::kPieceBins : 0;
+    const int n = len > 0 ? (len + P - 1) / P : 0;
+    s.max_q = std::max(s.max_q, n);
     int at = 0;
     for (int j = 0; j < n; ++j) {
       const int l = len / n + (j < len % n ? 1 : 0);
-      pieces.push_back(Piece{cfg->band_start[b] + at, l, (int)pieces.size(), cfg->band_weights + woff[b] + at});
+      rem.push_back(Piece{cfg->band_start[b] + at, l, b, j, cfg->band_weights + woff[b] + at});
       at += l;
     }
-    s.pstart[b + 1] = (int32_t)pieces.size();
   }
-  s.n_pieces = (int)pieces.size();
-  std::stable_sort(pieces.begin(), pieces.end(), [](const Piece& x, const Piece& y) { return x.len > y.len; });
-  const int n_passes = (s.n_pieces + 31) / 32;
-  s.start.assign(n_passes * 32, 0);
-  s.pid.assign(n_passes * 32, s.n_pieces);          // idle lanes dump into the spare slot
-  for (int ps = 0; ps < n_passes; ++ps) {
-    const int iters = pieces[ps * 32].len;
+  const int dump = s.max_q * s.b_pad;                  // idle lanes write here
+  std::stable_sort(rem.begin(), rem.end(), [](const Piece& x, const Piece& y) { return x.len > y.len; });
+  while (!rem.empty()) {
+    const int T = rem[0].len;
     const int off = (int)s.w.size();
-    s.pass.push_back(mmb::FbPass{iters, off});
-    s.w.resize(off + (size_t)iters * 32, 0.0f);
-    for (int l = 0; l < 32 && ps * 32 + l < s.n_pieces; ++l) {
-      const Piece& pc = pieces[ps * 32 + l];
-      int st = pc.start, lead = 0;
-      if (st + iters > K) { lead = st + iters - K; st -= lead; }      // keep every read inside the K magnitudes
-      s.start[ps * 32 + l] = st;
-      s.pid[ps * 32 + l] = pc.id;
-      for (int i = 0; i < pc.len; ++i) s.w[off + (size_t)(i + lead) * 32 + l] = pc.w[i];
+    const int ps = (int)s.pass.size();
+    s.pass.push_back(mmb::FbPass{T, off});
+    s.w.resize(off + (size_t)T * 32, 0.0f);
+    s.start.resize((ps + 1) * 32, 0);
+    s.pid.resize((ps + 1) * 32, dump);
+    bool lane_used[32] = {false};
+    int placed = 0;
+    std::vector<Piece> next;
+    for (size_t i = 0; i < rem.size(); ++i) {
+      const Piece& pc = rem[i];
+      bool ok = false;
+      if (placed < 32) {
+        for (int lead = 0; lead <= T - pc.len && !ok; ++lead) {
+          const int st = pc.start - lead;
+          if (st < 0 || st + T > K) continue;
+          const int lane = st & 31;
+          if (lane_used[lane]) continue;
+          lane_used[lane] = true; ++placed; ok = true;
+          s.start[ps * 32 + lane] = st;
+          s.pid[ps * 32 + lane] = pc.q * s.b_pad + pc.band;
+          for (int k = 0; k < pc.len; ++k) s.w[off + (size_t)(k + lead) * 32 + lane] = pc.w[k];
+        }
+        if (!ok && i == 0) {
+          // the pass-defining piece cannot stay inside [0, K) without a shift larger than its slack (only when
+          // T > K - start): shift it down as far as needed, bank conflicts or not
+          const int lead = std::max(0, pc.start + T - K);
+          int lane = (pc.start - lead) & 31;
+          while (lane_used[lane]) lane = (lane + 1) & 31;
+          lane_used[lane] = true; ++placed; ok = true;
+          s.start[ps * 32 + lane] = pc.start - lead;
+          s.pid[ps * 32 + lane] = pc.q * s.b_pad + pc.band;
+          s.w.resize(off + (size_t)(T + lead) * 32, 0.0f);
+          s.pass.back().iters = T + lead;
+          for (int k = 0; k < pc.len; ++k) s.w[off + (size_t)(k + lead) * 32 + lane] = pc.w[k];
+        }
+      }
+      if (!ok) next.push_back(pc);
     }
+    rem.swap(next);
   }
+  s.iters = 0;
+  for (const mmb::FbPass& fp : s.pass) s.iters += fp.iters;
+}
+
+void build_schedule(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, FbSchedule& best) {
+  static const int kCandidates[] = {8, 12, 16, 20, 24, 28, 32, 48, 64};
+  bool have = false;
+  for (int P : kCandidates) {
+    FbSchedule s;
+    schedule_with(cfg, K, woff, P, s);
+    if (s.max_q > 16) continue;
+    // cost: two shared-memory wavefronts per iteration plus the epilogue's max_q loads per 32 bands
+    const int cost = 2 * s.iters + s.max_q * (s.b_pad / 32);
+    const int best_cost = 2 * best.iters + best.max_q * (best.b_pad / 32);
+    if (!have || cost < best_cost) { best = s; have = true; }
+  }
+  if (!have) schedule_with(cfg, K, woff, 64, best);
 }
 }  // namespace
 
@@ -189,12 +236,12 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   }
   FbSchedule sch;
   build_schedule(cfg, K, woff, sch);
-  p->n_passes = (int)sch.pass.size(); p->n_pieces = sch.n_pieces; p->w_floats = (int)sch.w.size();
+  p->n_passes = (int)sch.pass.size(); p->max_q = sch.max_q; p->b_pad = sch.b_pad; p->w_floats = (int)sch.w.size();
+  p->fb_iters = sch.iters;
   if ((e = upload(&p->d_win, win)) != cudaSuccess || (e = upload(&p->d_tw1, tw1)) != cudaSuccess ||
       (e = upload(&p->d_tw2k, tw2k)) != cudaSuccess || (e = upload(&p->d_tw4k, tw4k)) != cudaSuccess ||
       (e = upload(&p->d_pass, sch.pass)) != cudaSuccess || (e = upload(&p->d_fbw, sch.w)) != cudaSuccess ||
-      (e = upload(&p->d_fbstart, sch.start)) != cudaSuccess || (e = upload(&p->d_fbpid, sch.pid)) != cudaSuccess ||
-      (e = upload(&p->d_pstart, sch.pstart)) != cudaSuccess) {
+      (e = upload(&p->d_fbstart, sch.start)) != cudaSuccess || (e = upload(&p->d_fbpid, sch.pid)) != cudaSuccess) {
     mmb_plan_destroy(p);
     return cuda_fail(e, "plan constant upload");
   }
@@ -205,7 +252,7 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
     const int fpr = mmb::frames_per_round(N, w);
     const int span = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N + align_elems) + 7) & ~7;
     const int rows = 2 * fpr + cfg->diff_frames;
-    const mmb::SmemLayout L = mmb::smem_layout(N, w, cfg->num_bands, p->n_passes, p->n_pieces, p->w_floats, rows, span,
+    const mmb::SmemLayout L = mmb::smem_layout(N, w, cfg->num_bands, p->n_passes, p->max_q * p->b_pad, p->w_floats, rows, span,
                                                p->sample_bytes);
     if (L.total <= (int)prop.sharedMemPerBlockOptin) {
       p->warps = w; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
@@ -307,9 +354,8 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.win = p->d_win; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
   const bool band_out = o->filt || o->log || o->diff || o->odf;
   fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only stft/spec are wanted
-  fp.n_passes = p->n_passes; fp.n_pieces = p->n_pieces; fp.w_floats = p->w_floats;
+  fp.n_passes = p->n_passes; fp.max_q = p->max_q; fp.b_pad = p->b_pad; fp.w_floats = p->w_floats;
   fp.fb_pass = p->d_pass; fp.fb_w = p->d_fbw; fp.fb_start = p->d_fbstart; fp.fb_pid = p->d_fbpid;
-  fp.band_pstart = p->d_pstart;
   fp.pcm_extent = pcm_extent; fp.bulk_allowed = ((uintptr_t)pcm_dev % 16) == 0;
   fp.warps = p->warps; fp.ring_rows = p->ring_rows;
   fp.mul = p->cfg.mul; fp.add = p->cfg.add; fp.log_mode = p->cfg.log_mode;

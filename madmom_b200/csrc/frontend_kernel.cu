@@ -123,7 +123,8 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
                                                 const float* __restrict__ mag1, float* part,
                                                 const FbPass* __restrict__ s_pass, const float* __restrict__ s_w,
                                                 const int* __restrict__ s_start, const int* __restrict__ s_pid) {
-  const int np1 = p.n_pieces + 1;
+  // the previous frame's epilogue reads of `part` are complete: the warp has passed a __syncwarp since
+  const int np1 = p.max_q * p.b_pad + 1;
   for (int ps = 0; ps < p.n_passes; ++ps) {
     const FbPass fp = s_pass[ps];
     const int st = s_start[ps * 32 + lane];
@@ -146,13 +147,11 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
 
 // rows of the ring / outputs for one frame g handled by this warp
 __device__ __forceinline__ void warp_band_epilogue(const FrontendParams& p, int lane, const float* part,
-                                                   const int* __restrict__ s_pstart, float* ring_row, long long row,
-                                                   bool emit) {
-  const int nb = p.n_bands;
+                                                   float* ring_row, long long row, bool emit) {
+  const int nb = p.n_bands, bp = p.b_pad, nq = p.max_q;
   for (int b = lane; b < nb; b += 32) {
-    const int q0 = s_pstart[b], q1 = s_pstart[b + 1];
-    float acc = 0.0f;
-    for (int q = q0; q < q1; ++q) acc += part[q];
+    float acc = part[b];
+    for (int q = 1; q < nq; ++q) acc += part[q * bp + b];     // slots without a piece stay zero
     if (emit && p.out_filt) p.out_filt[row * p.ld_filt + b] = acc;
     ring_row[b] = p.log_mode != 0 ? log_scaled(acc, p.log_mode, p.mul, p.add) : acc;
   }
@@ -173,7 +172,9 @@ __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lan
     float dv = 0.0f;
     if (has_prev) {
       float ref;
-      if (m > 1) {                                       // scipy maximum_filter, mode='reflect'
+      if (m == 3) {                                      // the SuperFlux case, 'reflect' duplicates the edge bin
+        ref = fmaxf(fmaxf(prev[b > 0 ? b - 1 : 0], prev[b]), prev[b + 1 < nb ? b + 1 : nb - 1]);
+      } else if (m > 1) {                                // scipy maximum_filter, mode='reflect'
         ref = -INFINITY;
         for (int j = 0; j < m; ++j) {
           int q = b - half + j;
@@ -204,8 +205,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nthreads = blockDim.x, warps = nthreads >> 5;
   const int FPR = frames_per_round(N, warps);
-  const SmemLayout L = smem_layout(N, warps, p.n_bands, p.n_passes, p.n_pieces, p.w_floats, p.ring_rows, p.span_cap,
-                                   (int)sizeof(S));
+  const SmemLayout L = smem_layout(N, warps, p.n_bands, p.n_passes, p.max_q * p.b_pad, p.w_floats, p.ring_rows,
+                                   p.span_cap, (int)sizeof(S));
   uint64_t* s_mbar = reinterpret_cast<uint64_t*>(smem + L.mbar);
   RoundDesc* s_desc = reinterpret_cast<RoundDesc*>(smem + L.desc);
   float* s_win = reinterpret_cast<float*>(smem + L.win);
@@ -216,7 +217,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   float* s_w = reinterpret_cast<float*>(smem + L.fb_w);
   int* s_start = reinterpret_cast<int*>(smem + L.fb_start);
   int* s_pid = reinterpret_cast<int*>(smem + L.fb_pid);
-  int* s_pstart = reinterpret_cast<int*>(smem + L.band_pstart);
   float* s_ring = reinterpret_cast<float*>(smem + L.ring);
   const int pcm_stride = mmb_align16(p.span_cap * (int)sizeof(S));
 
@@ -238,7 +238,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     for (int i = tid; i < p.n_passes; i += nthreads) s_pass[i] = p.fb_pass[i];
     for (int i = tid; i < p.w_floats; i += nthreads) s_w[i] = p.fb_w[i];
     for (int i = tid; i < p.n_passes * 32; i += nthreads) { s_start[i] = p.fb_start[i]; s_pid[i] = p.fb_pid[i]; }
-    for (int i = tid; i <= nb; i += nthreads) s_pstart[i] = p.band_pstart[i];
+    for (int i = tid; i < warps * (L.part_stride / 4); i += nthreads)
+      reinterpret_cast<float*>(smem + L.part)[i] = 0.0f;     // part slots without a piece are never written again
   }
   if (tid == 0) {
     mbar_init(&s_mbar[0], 1);
@@ -330,10 +331,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
             __syncwarp();
             warp_filterbank<2>(p, lane, my_mag, my_mag + 512, my_part, s_pass, s_w, s_start, s_pid);
             int sa = slot0 + fa; if (sa >= R) sa -= R;
-            warp_band_epilogue(p, lane, my_part, s_pstart, s_ring + sa * nb, rowA, gA >= ga);
+            warp_band_epilogue(p, lane, my_part, s_ring + sa * nb, rowA, gA >= ga);
             if (haveB) {
               int sb = sa + 1; if (sb >= R) sb -= R;
-              warp_band_epilogue(p, lane, my_part + p.n_pieces + 1, s_pstart, s_ring + sb * nb, rowB, gB >= ga);
+              warp_band_epilogue(p, lane, my_part + p.max_q * p.b_pad + 1, s_ring + sb * nb, rowB, gB >= ga);
             }
           }
         }
@@ -374,7 +375,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           __syncwarp();
           warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
           int sl = slot0 + warp; if (sl >= R) sl -= R;
-          warp_band_epilogue(p, lane, my_part, s_pstart, s_ring + sl * nb, row, g >= ga);
+          warp_band_epilogue(p, lane, my_part, s_ring + sl * nb, row, g >= ga);
         }
       }
     }

@@ -16,16 +16,14 @@ struct Track {
   int64_t out_row;       // first output row of this unit
 };
 
-// Per-warp filterbank schedule (built on the host, capi.cu): every band is cut into pieces of at most
-// kPieceBins bins; pieces are sorted by length and dealt to the 32 lanes pass by pass.  In pass p lane l
-// accumulates   sum_i mag[start[p][l] + i] * w[p][i][l],  i < iters[p]   (weights zero-padded to iters[p]),
-// stores the partial sum at part[pid[p][l]], and a second step adds the pieces of each band in order.
+// Per-warp filterbank schedule (built on the host, capi.cu): every band is cut into pieces; in pass p lane l
+// accumulates   sum_i mag[start[p][l] + i] * w[p][i][l],  i < iters[p]   (weights zero-padded to iters[p]; the
+// starts of a pass are distinct modulo 32, so the reads are free of bank conflicts) and stores the partial sum at
+// part[pid[p][l]] = part[q * b_pad + band]; the epilogue adds the pieces q = 0 .. max_q-1 of each band in order.
 struct FbPass {
   int32_t iters;   // loop length of this pass (length of its longest piece)
   int32_t woff;    // offset (floats) of w[p][0][0] inside the weight table
 };
-constexpr int kPieceBins = 16;
-constexpr int kMaxPasses = 16;
 
 struct FrontendParams {
   const void* pcm;               // int16 or float32 samples
@@ -46,12 +44,11 @@ struct FrontendParams {
   const float2* tw2k;            // 1024: W2048^k (N = 2048 uses the first 512)
   const float2* tw4k;            // 512 : W4096^(2j+1)
   int32_t n_bands;               // 0 -> no filterbank stage
-  int32_t n_passes, n_pieces, w_floats;
+  int32_t n_passes, max_q, b_pad, w_floats;
   const FbPass* fb_pass;         // [n_passes]
   const float* fb_w;             // [w_floats]
   const int32_t* fb_start;       // [n_passes * 32]
-  const int32_t* fb_pid;         // [n_passes * 32] piece id, n_pieces for idle lanes
-  const int32_t* band_pstart;    // [n_bands + 1] pieces of band b are part[pstart[b] .. pstart[b+1])
+  const int32_t* fb_pid;         // [n_passes * 32] q * b_pad + band, max_q * b_pad for idle lanes
   float mul, add;
   int32_t log_mode;              // 0 none, 1 log10, 2 mul/add only, 3 ln, 4 log2
   int32_t diff_frames;           // d >= 1 when a difference is requested
@@ -95,13 +92,13 @@ struct RoundDesc {
 };
 
 struct SmemLayout {
-  int mbar, desc, win, tw1, tw2k, tw4k, fb_pass, fb_w, fb_start, fb_pid, band_pstart, ring, scratch, part, pcm, total;
+  int mbar, desc, win, tw1, tw2k, tw4k, fb_pass, fb_w, fb_start, fb_pid, ring, scratch, part, pcm, total;
   int part_stride;       // bytes of partial sums per warp
 };
 
 __host__ __device__ inline int mmb_align16(int x) { return (x + 15) & ~15; }
 
-__host__ __device__ inline SmemLayout smem_layout(int N, int warps, int n_bands, int n_passes, int n_pieces,
+__host__ __device__ inline SmemLayout smem_layout(int N, int warps, int n_bands, int n_passes, int part_floats,
                                                   int w_floats, int ring_rows, int span_cap, int sample_bytes) {
   SmemLayout L;
   int o = 0;
@@ -115,10 +112,9 @@ __host__ __device__ inline SmemLayout smem_layout(int N, int warps, int n_bands,
   L.fb_w = o;        o += mmb_align16(w_floats * 4);
   L.fb_start = o;    o += mmb_align16(n_passes * 32 * 4);
   L.fb_pid = o;      o += mmb_align16(n_passes * 32 * 4);
-  L.band_pstart = o; o += mmb_align16(n_bands > 0 ? (n_bands + 1) * 4 : 0);
   L.ring = o;        o += mmb_align16(n_bands > 0 ? ring_rows * n_bands * 4 : 0);
   L.scratch = o;     o += warps * warp_scratch_bytes(N);
-  L.part_stride = mmb_align16((n_pieces + 1) * 4 * (N == 1024 ? 2 : 1));
+  L.part_stride = mmb_align16((part_floats + 1) * 4 * (N == 1024 ? 2 : 1));
   L.part = o;        o += n_bands > 0 ? warps * L.part_stride : 0;
   L.pcm = o;         o += 2 * mmb_align16(span_cap * sample_bytes);
   L.total = o;

@@ -76,6 +76,13 @@ __global__ void __launch_bounds__(256) rate_probe(float* out, int iters, float a
       else if (WHICH == 4) {
         const float2 w = sm[(threadIdx.x + 32 * i + it) & 511];
         acc[i] = fmaf(acc[i], w.x, w.y); acc[i] = fmaf(acc[i], x[i], w.x);
+      } else if (WHICH == 5) {           // LDS.32 only (conflict-free)
+        acc[i] += reinterpret_cast<const float*>(sm)[(threadIdx.x + 32 * i + it) & 1023];
+      } else if (WHICH == 6) {           // SHFL only
+        acc[i] = __shfl_sync(0xffffffffu, acc[i], (threadIdx.x + i + 1) & 31) + x[i];
+      } else if (WHICH == 7) {           // one LDS.32 + one SHFL per step
+        acc[i] = __shfl_sync(0xffffffffu, acc[i], (threadIdx.x + i + 1) & 31) +
+                 reinterpret_cast<const float*>(sm)[(threadIdx.x + 32 * i + it) & 1023];
       }
     }
   }
@@ -89,7 +96,7 @@ __global__ void __launch_bounds__(256) rate_probe(float* out, int iters, float a
 // result: warp-level FP instructions per clock per SM at the current clock estimate is left to the caller;
 // *ginst_per_s receives 1e9 thread-level FP instructions per second (whole device).
 extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s) {
-  if (!ginst_per_s || which < 1 || which > 4) return MMB_E_INVALID;
+  if (!ginst_per_s || which < 1 || which > 7) return MMB_E_INVALID;
   if (cudaSetDevice(device) != cudaSuccess) return MMB_E_CUDA;
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return MMB_E_CUDA;
@@ -104,7 +111,10 @@ extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* gin
     if (which == 1) rate_probe<1><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     else if (which == 2) rate_probe<2><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     else if (which == 3) rate_probe<3><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
-    else rate_probe<4><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 4) rate_probe<4><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 5) rate_probe<5><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 6) rate_probe<6><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else rate_probe<7><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     cudaEventRecord(e1);
     if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return MMB_E_CUDA; }
     float ms = 0.f;

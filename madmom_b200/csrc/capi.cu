@@ -116,7 +116,7 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
   const int dump = s.max_q * s.b_pad;                  // idle lanes write here
   std::stable_sort(rem.begin(), rem.end(), [](const Piece& x, const Piece& y) { return x.len > y.len; });
   while (!rem.empty()) {
-    const int T = rem[0].len;
+    const int T = std::min((rem[0].len + 3) & ~3, K & ~3);      // pass lengths are multiples of four
     const int off = (int)s.w.size();
     const int ps = (int)s.pass.size();
     s.pass.push_back(mmb::FbPass{T, off});
@@ -149,8 +149,6 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
           lane_used[lane] = true; ++placed; ok = true;
           s.start[ps * 32 + lane] = pc.start - lead;
           s.pid[ps * 32 + lane] = pc.q * s.b_pad + pc.band;
-          s.w.resize(off + (size_t)(T + lead) * 32, 0.0f);
-          s.pass.back().iters = T + lead;
           for (int k = 0; k < pc.len; ++k) s.w[off + (size_t)(k + lead) * 32 + lane] = pc.w[k];
         }
       }

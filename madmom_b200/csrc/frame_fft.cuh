@@ -78,7 +78,8 @@ MMB_HD float log_scaled(float x, int mode, float mul, float add) {
 // Output sink: magnitudes into warp scratch `mag` (always), and optionally complex bins / magnitudes
 // straight to global memory (row pointers, may be null).  `sgn_odd` = -1 when circular_shift is set:
 // swapping the two halves of the frame multiplies X[k] by (-1)^k (madmom/audio/stft.py:106-119).
-struct BinSink {
+template <bool EMIT>
+struct BinSinkT {
   float* mag;        // warp scratch, K floats
   float2* stft_row;  // global, K complex, or null
   float* spec_row;   // global, K floats, or null
@@ -88,6 +89,7 @@ struct BinSink {
   MMB_HD void put(int k, float re, float im) const {
     const float m = mag_of(re, im);
     mag[k] = m;
+    if (!EMIT) return;                 // hot path: magnitudes stay on chip, no per-bin branches
     if (spec_row) spec_row[k] = log_mode ? log_scaled(m, log_mode, mul, add) : m;
     if (stft_row) {
       const float s = (k & 1) ? sgn_odd : 1.0f;
@@ -95,10 +97,14 @@ struct BinSink {
     }
   }
 };
+using BinSink = BinSinkT<true>;
+MMB_HD BinSinkT<false> quiet(const BinSink& o) { BinSinkT<false> q; q.mag = o.mag; q.stft_row = nullptr; q.spec_row = nullptr; q.sgn_odd = 1.0f; q.log_mode = 0; q.mul = 1.0f; q.add = 0.0f; return q; }
+
 
 // N = 2048.  v[r] = Z[lane + 32 brev5(r)], zs[k] valid for k in [512, 1024]  (zs[1024] = Z[0]).
+template <class Sink>
 MMB_HD void split_2048(int lane, const float2 (&v)[32], const float2* zs, const float2* __restrict__ tw2k,
-                       const BinSink& out) {
+                       const Sink& out) {
 #pragma unroll
   for (int q = 0; q < 16; ++q) {
     const float2 zk = v[brev5(q)];
@@ -118,8 +124,9 @@ MMB_HD void split_2048(int lane, const float2 (&v)[32], const float2* zs, const 
 }
 
 // N = 1024, two frames.  Bins of frame A via outA, frame B via outB (k in [0, 512)).
-MMB_HD void split_1024x2(int lane, const float2 (&v)[32], const float2* zs, const BinSink& outA,
-                         const BinSink& outB, bool haveB) {
+template <class Sink>
+MMB_HD void split_1024x2(int lane, const float2 (&v)[32], const float2* zs, const Sink& outA,
+                         const Sink& outB, bool haveB) {
 #pragma unroll
   for (int q = 0; q < 16; ++q) {
     const float2 zk = v[brev5(q)];
@@ -132,8 +139,9 @@ MMB_HD void split_1024x2(int lane, const float2 (&v)[32], const float2* zs, cons
 
 // N = 4096, half c.  Even bins (c = 0) pair as (j, 1024 - j) with twiddle W4096^(2j) = W2048^j;
 // odd bins (c = 1) pair as (j, 1023 - j) with twiddle W4096^(2j+1) = tw4k[q*32 + lane].
+template <class Sink>
 MMB_HD void split_4096(int lane, int c, const float2 (&v)[32], const float2* zs,
-                       const float2* __restrict__ tw2k, const float2* __restrict__ tw4k, const BinSink& out) {
+                       const float2* __restrict__ tw2k, const float2* __restrict__ tw4k, const Sink& out) {
 #pragma unroll
   for (int q = 0; q < 16; ++q) {
     const float2 zk = v[brev5(q)];

@@ -130,13 +130,19 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
     const int st = s_start[ps * 32 + lane];
     const float* w = s_w + fp.woff + lane;
     const float* m0 = mag0 + st;
-    const float* m1 = mag1 + st;
+    const float* m1 = (NF == 2) ? mag1 + st : mag0;
     float a0 = 0.0f, a1 = 0.0f;
-#pragma unroll 4
-    for (int i = 0; i < fp.iters; ++i) {
-      const float wi = w[i * 32];
-      a0 = fmaf(m0[i], wi, a0);
-      if (NF == 2) a1 = fmaf(m1[i], wi, a1);
+#pragma unroll 1
+    for (int i = 0; i < fp.iters; i += 4) {          // pass lengths are multiples of four (capi.cu)
+      const float w0 = w[0], w1 = w[32], w2 = w[64], w3 = w[96];
+      const float x0 = m0[0], x1 = m0[1], x2 = m0[2], x3 = m0[3];
+      a0 = fmaf(x0, w0, a0); a0 = fmaf(x1, w1, a0); a0 = fmaf(x2, w2, a0); a0 = fmaf(x3, w3, a0);
+      if (NF == 2) {
+        const float y0 = m1[0], y1 = m1[1], y2 = m1[2], y3 = m1[3];
+        a1 = fmaf(y0, w0, a1); a1 = fmaf(y1, w1, a1); a1 = fmaf(y2, w2, a1); a1 = fmaf(y3, w3, a1);
+        m1 += 4;
+      }
+      w += 128; m0 += 4;
     }
     const int pid = s_pid[ps * 32 + lane];
     part[pid] = a0;
@@ -324,7 +330,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
           oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
           ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
-          split_1024x2(lane, v, ex, oa, ob, haveB);
+          if (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row) split_1024x2(lane, v, ex, oa, ob, haveB);
+          else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
           if (nb > 0) {
             __syncwarp();
             if (!haveB) for (int i = lane; i < 512; i += 32) my_mag[512 + i] = 0.0f;
@@ -355,7 +362,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           core_pass2_fft(v);
           core_publish_upper(lane, v, ex, true);
           __syncwarp();
-          split_2048(lane, v, ex, s_tw2k, o);
+          if (o.stft_row || o.spec_row) split_2048(lane, v, ex, s_tw2k, o);
+          else split_2048(lane, v, ex, s_tw2k, quiet(o));
         } else {
 #pragma unroll 1
           for (int c = 0; c < 2; ++c) {
@@ -367,7 +375,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
             core_pass2_fft(v);
             core_publish_upper(lane, v, ex, c == 0);
             __syncwarp();
-            split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
+            if (o.stft_row || o.spec_row) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
+            else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
             __syncwarp();
           }
         }

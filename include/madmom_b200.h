@@ -95,6 +95,9 @@ typedef struct mmb_outputs {
   float* log;  int64_t ld_log;   /* log-filtered spectrogram (rows, num_bands)  */
   float* diff; int64_t ld_diff;  /* (positive, max-filtered) difference         */
   float* odf;                    /* row sums of diff (rows)                     */
+  float* lgd;  int64_t ld_lgd;   /* |local group delay| / pi per bin (rows, frame_size/2), frame_size 2048 only:
+                                    |unwrap(phase)[k] - unwrap(phase)[k+1]| / pi, last bin 0 (stft.py:154-179,
+                                    onsets.py:282-284); input of mmb_complex_flux                              */
 } mmb_outputs;
 
 typedef struct mmb_plan_info {
@@ -151,6 +154,16 @@ MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg_offsets_de
                              double threshold, int32_t smooth, const double* smooth_kernel_dev, int32_t pre_avg,
                              int32_t post_avg, int32_t pre_max, int32_t post_max, int32_t* peaks_dev,
                              int32_t* counts_dev, void* stream);
+
+/* complex_flux() of madmom/features/onsets.py:245-317 from the lgd and diff outputs of mmb_run:
+ * temporal maximum filter of width temporal_filter (odd, reflect borders inside each signal; <= 1: none) on lgd,
+ * mask[b] = min over bins [band_lo[b], band_hi[b]) (the band's non-zero bins plus one either side, clipped),
+ * odf[row] = sum_b diff[row, b] * mask[b].  Signals are either equal-length (rows_per_signal > 0), given by
+ * seg_offsets_dev[n_segments + 1], or the whole matrix is one signal. */
+MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, const float* diff_dev, int64_t ld_diff,
+                             const int32_t* band_lo_dev, const int32_t* band_hi_dev, int32_t n_bands, int32_t n_bins,
+                             int64_t rows, int64_t rows_per_signal, const int64_t* seg_offsets_dev, int32_t n_segments,
+                             int32_t temporal_filter, float* odf_dev, void* stream);
 
 /* Calibration: measured FP32 FMA throughput of `device` in TFLOP/s (dependent FFMA chains on every SM,
  * best of 5, CUDA events).  The front end is FP32-pipe bound; bench.py reports its roofline against this. */

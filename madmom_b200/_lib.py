@@ -37,7 +37,7 @@ TRACK_DTYPE = np.dtype([("pcm_offset", "<i8"), ("pcm_len", "<i8"), ("sample_base
 class Outputs(ctypes.Structure):
     _fields_ = [("stft", c_vp), ("ld_stft", c_i64), ("spec", c_vp), ("ld_spec", c_i64), ("filt", c_vp),
                 ("ld_filt", c_i64), ("log", c_vp), ("ld_log", c_i64), ("diff", c_vp), ("ld_diff", c_i64),
-                ("odf", c_vp)]
+                ("odf", c_vp), ("lgd", c_vp), ("ld_lgd", c_i64)]
 
 
 class PlanInfo(ctypes.Structure):
@@ -62,6 +62,8 @@ EXPORTS = {
     "mmb_measure_fp32_peak": (c_i32, [c_i32, ctypes.POINTER(c_f64)]),
     "mmb_rate_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
     "mmb_matrix_diff": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i32, c_i64, c_i32, c_i32, c_i32, c_vp]),
+    "mmb_complex_flux": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_i32, c_i32, c_i64, c_i64, c_vp, c_i32, c_i32,
+                                 c_vp, c_vp]),
     "mmb_peak_picking": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp,
                                  c_vp, c_vp]),
 }
@@ -154,7 +156,7 @@ def make_units(num_samples, frame_counts, pcm_offsets=None, sample_base=None, fr
     return u
 
 
-OUTPUT_NAMES = ("stft", "spec", "filt", "log", "diff", "odf")
+OUTPUT_NAMES = ("stft", "spec", "filt", "log", "diff", "odf", "lgd")
 
 
 class FrontEndPlan(object):
@@ -213,7 +215,7 @@ class FrontEndPlan(object):
             pass
 
     def width(self, name):
-        return {"stft": self.num_bins, "spec": self.num_bins, "odf": 1}.get(name, self.num_bands)
+        return {"stft": self.num_bins, "spec": self.num_bins, "lgd": self.num_bins, "odf": 1}.get(name, self.num_bands)
 
     def _layout(self, units):
         key = units.tobytes()
@@ -342,3 +344,22 @@ def peak_picking(act, threshold, smooth=0, pre_avg=0, post_avg=0, pre_max=1, pos
         raise ValueError("mmb_peak_picking: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_peak_picking failed")
     launch_count += 2 if n else 1
     return peaks, counts
+
+
+def complex_flux(lgd, diff, band_lo, band_hi, temporal_filter=3, rows_per_signal=0, seg_offsets=None):
+    """mmb_complex_flux: lgd (rows, K), diff (rows, B) float32 CUDA tensors, band_lo/hi int32 CUDA tensors [B].
+    Returns the (rows,) onset detection function on the device."""
+    global launch_count
+    import torch
+    rows, K = lgd.shape
+    B = diff.shape[1]
+    odf = torch.empty((rows,), dtype=torch.float32, device=lgd.device)
+    n_seg = 0 if seg_offsets is None else int(seg_offsets.shape[0]) - 1
+    rc = load().mmb_complex_flux(lgd.data_ptr(), lgd.stride(0), diff.data_ptr(), diff.stride(0), band_lo.data_ptr(),
+                                 band_hi.data_ptr(), B, K, rows, int(rows_per_signal),
+                                 None if seg_offsets is None else seg_offsets.data_ptr(), n_seg,
+                                 int(temporal_filter), odf.data_ptr(), _stream(lgd.device.index))
+    if rc != MMB_OK:
+        raise ValueError("mmb_complex_flux: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_complex_flux failed")
+    launch_count += 1 if rows else 0
+    return odf

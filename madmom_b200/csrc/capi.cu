@@ -335,7 +335,9 @@ extern "C" int mmb_layout_create(const mmb_plan* p, const mmb_track* units, int3
 static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
   if (!o) return fail(MMB_E_INVALID, "outputs is null");
   const bool band_out = o->filt || o->log || o->diff || o->odf;
-  if (!o->stft && !o->spec && !band_out) return fail(MMB_E_INVALID, "no output requested");
+  if (!o->stft && !o->spec && !band_out && !o->lgd) return fail(MMB_E_INVALID, "no output requested");
+  if (o->lgd && p->cfg.frame_size != 2048)
+    return fail(MMB_E_UNSUPPORTED, "the local group delay output is implemented for frame_size 2048 only");
   if (band_out && p->cfg.num_bands == 0)
     return fail(MMB_E_UNSUPPORTED, "filt/log/diff/odf outputs need a filterbank in the plan");
   if ((o->diff || o->odf) && p->cfg.diff_frames < 1)
@@ -363,6 +365,7 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.out_stft = (float2*)o->stft; fp.ld_stft = o->ld_stft; fp.out_spec = o->spec; fp.ld_spec = o->ld_spec;
   fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
   fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;
+  fp.out_lgd = o->lgd; fp.ld_lgd = o->ld_lgd;
   int grid = p->num_sms;                              // one persistent CTA per SM
   if (grid > chunks) grid = chunks;
   if (grid < 1) return MMB_OK;
@@ -404,7 +407,7 @@ constexpr int64_t kGroupBytes = 64ll << 20;
 struct Slot {
   cudaStream_t stream = nullptr;
   void* d_pcm = nullptr; size_t pcm_cap = 0;
-  void* d_out[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; size_t out_cap[6] = {0, 0, 0, 0, 0, 0};
+  void* d_out[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; size_t out_cap[7] = {0, 0, 0, 0, 0, 0, 0};
   Track* d_tracks = nullptr; size_t tracks_cap = 0;
   int32_t* d_prefix = nullptr; size_t prefix_cap = 0;
 };
@@ -434,11 +437,11 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
   const int K = p->cfg.frame_size / 2, B = p->cfg.num_bands;
   const size_t sb = (size_t)p->sample_bytes;
   // widths (elements) and element sizes of the six outputs: stft spec filt log diff odf
-  void* hptr[6] = {oh->stft, oh->spec, oh->filt, oh->log, oh->diff, oh->odf};
-  const int64_t hld[6] = {oh->ld_stft, oh->ld_spec, oh->ld_filt, oh->ld_log, oh->ld_diff, 1};
-  const int width[6] = {K, K, B, B, B, 1};
-  const size_t esz[6] = {8, 4, 4, 4, 4, 4};
-  for (int k = 0; k < 6; ++k)
+  void* hptr[7] = {oh->stft, oh->spec, oh->filt, oh->log, oh->diff, oh->odf, oh->lgd};
+  const int64_t hld[7] = {oh->ld_stft, oh->ld_spec, oh->ld_filt, oh->ld_log, oh->ld_diff, 1, oh->ld_lgd};
+  const int width[7] = {K, K, B, B, B, 1, K};
+  const size_t esz[7] = {8, 4, 4, 4, 4, 4, 4};
+  for (int k = 0; k < 7; ++k)
     if (hptr[k] && hld[k] < width[k]) return fail(MMB_E_INVALID, "leading dimension smaller than the row width");
 
   Slot slots[kSlots];
@@ -448,7 +451,7 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
     for (int s = 0; s < kSlots; ++s) {
       if (slots[s].stream) { cudaStreamSynchronize(slots[s].stream); cudaStreamDestroy(slots[s].stream); }
       cudaFree(slots[s].d_pcm); cudaFree(slots[s].d_tracks); cudaFree(slots[s].d_prefix);
-      for (int k = 0; k < 6; ++k) cudaFree(slots[s].d_out[k]);
+      for (int k = 0; k < 7; ++k) cudaFree(slots[s].d_out[k]);
     }
   };
 #define CUS(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { status = cuda_fail(e_, #x); goto done; } } while (0)
@@ -490,7 +493,7 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
       CUS(ensure((void**)&S.d_prefix, &S.prefix_cap, prefix.size() * sizeof(int32_t)));
       mmb_outputs od;
       std::memset(&od, 0, sizeof(od));
-      for (int k = 0; k < 6; ++k) {
+      for (int k = 0; k < 7; ++k) {
         if (!hptr[k]) continue;
         CUS(ensure(&S.d_out[k], &S.out_cap[k], (size_t)(rows > 0 ? rows : 1) * width[k] * esz[k]));
       }
@@ -500,6 +503,7 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
       od.log = hptr[3] ? (float*)S.d_out[3] : nullptr; od.ld_log = B;
       od.diff = hptr[4] ? (float*)S.d_out[4] : nullptr; od.ld_diff = B;
       od.odf = hptr[5] ? (float*)S.d_out[5] : nullptr;
+      od.lgd = hptr[6] ? (float*)S.d_out[6] : nullptr; od.ld_lgd = K;
       CUS(cudaMemcpyAsync(S.d_tracks, tab.data(), tab.size() * sizeof(Track), cudaMemcpyHostToDevice, S.stream));
       CUS(cudaMemcpyAsync(S.d_prefix, prefix.data(), prefix.size() * sizeof(int32_t), cudaMemcpyHostToDevice, S.stream));
       CUS(cudaMemcpyAsync(S.d_pcm, (const char*)pcm_host + (size_t)pcm0 * sb, (size_t)(pcm1 - pcm0) * sb,
@@ -511,7 +515,7 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
                         S.stream);
         if (status) goto done;
         ++n_launch;
-        for (int k = 0; k < 6; ++k) {
+        for (int k = 0; k < 7; ++k) {
           if (!hptr[k]) continue;
           char* dst = (char*)hptr[k] + (size_t)row0 * hld[k] * esz[k];
           CUS(cudaMemcpy2DAsync(dst, (size_t)hld[k] * esz[k], S.d_out[k], (size_t)width[k] * esz[k],

@@ -123,6 +123,54 @@ MMB_HD void split_2048(int lane, const float2 (&v)[32], const float2* zs, const 
   }
 }
 
+#if defined(__CUDACC__)
+// |angle(a * conj(b))| / pi in [0, 1]; `flip` = -1 negates the product (circular shift: X[k] -> (-1)^k X[k]).
+__device__ __forceinline__ float abs_angle_over_pi(float2 a, float2 b, float flip) {
+  const float re = (a.x * b.x + a.y * b.y) * flip;
+  const float im = a.y * b.x - a.x * b.y;
+  return atan2f(fabsf(im), re) / 3.14159265358979323846f;
+}
+
+// N = 2048 split that also emits the magnitude of the local group delay (ComplexFlux, madmom/audio/stft.py:
+// 154-179 and madmom/features/onsets.py:282-284):  lgd[k] = |unwrap(phase)[k] - unwrap(phase)[k+1]| / pi, last bin
+// 0.  The difference of neighbouring unwrapped phases is the principal value of the phase difference, i.e.
+// |angle(X[k+1] conj X[k])|, so no scan along the bins is needed.  Bins are walked from high q to low q so that
+// the neighbour of lane 31 (bin 32(q+1), owned by lane 0) is already known; neighbours travel by warp shuffle.
+template <class Sink>
+__device__ __forceinline__ void split_2048_lgd(int lane, const float2 (&v)[32], const float2* zs,
+                                               const float2* __restrict__ tw2k, const Sink& out,
+                                               float* __restrict__ lgd_row, float flip) {
+  const float2 z512 = v[brev5(16)];
+  const float2 x512 = make_float2(2.0f * z512.x, -2.0f * z512.y);       // meaningful in lane 0 only
+  if (lane == 0) out.put(512, x512.x, x512.y);
+  float2 prev_lo = x512, prev_hi = x512;
+  const int up = (lane + 1) & 31;
+#pragma unroll
+  for (int q = 15; q >= 0; --q) {
+    const float2 zk = v[brev5(q)];
+    const int k = lane + 32 * q, kp = 1024 - k;
+    const float2 zp = zs[kp];
+    const float2 w = tw2k[q * 32 + lane];
+    const float ar = zk.x + zp.x, ai = zk.y - zp.y;
+    const float br = zk.x - zp.x, bi = zk.y + zp.y;
+    const float tr = w.x * br - w.y * bi, ti = w.x * bi + w.y * br;
+    const float2 xk = make_float2(ar + ti, ai - tr);
+    const float2 xp = make_float2(ar - ti, -(ai + tr));                  // X[1024 - k]
+    out.put(k, xk.x, xk.y);
+    if (kp < 1024) out.put(kp, xp.x, xp.y);
+    // lane 0 hands lane 31 its bins of the previous (higher) q
+    const float2 give_lo = lane == 0 ? prev_lo : xk;
+    const float2 give_hi = lane == 0 ? prev_hi : xp;
+    float2 nlo, nhi;
+    nlo.x = __shfl_sync(0xffffffffu, give_lo.x, up); nlo.y = __shfl_sync(0xffffffffu, give_lo.y, up);
+    nhi.x = __shfl_sync(0xffffffffu, give_hi.x, up); nhi.y = __shfl_sync(0xffffffffu, give_hi.y, up);
+    lgd_row[k] = abs_angle_over_pi(nlo, xk, flip);                       // X[k+1] against X[k]
+    lgd_row[kp - 1] = (kp == 1024) ? 0.0f : abs_angle_over_pi(xp, nhi, flip);   // X[kp] against X[kp-1]
+    prev_lo = xk; prev_hi = xp;
+  }
+}
+#endif
+
 // N = 1024, two frames.  Bins of frame A via outA, frame B via outB (k in [0, 512)).
 template <class Sink>
 MMB_HD void split_1024x2(int lane, const float2 (&v)[32], const float2* zs, const Sink& outA,

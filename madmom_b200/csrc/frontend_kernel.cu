@@ -362,8 +362,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           core_pass2_fft(v);
           core_publish_upper(lane, v, ex, true);
           __syncwarp();
-          if (o.stft_row || o.spec_row) split_2048(lane, v, ex, s_tw2k, o);
-          else split_2048(lane, v, ex, s_tw2k, quiet(o));
+          if (p.out_lgd && g >= ga) {
+            split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
+          } else if (o.stft_row || o.spec_row) {
+            split_2048(lane, v, ex, s_tw2k, o);
+          } else {
+            split_2048(lane, v, ex, s_tw2k, quiet(o));
+          }
         } else {
 #pragma unroll 1
           for (int c = 0; c < 2; ++c) {

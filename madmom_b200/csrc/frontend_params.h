@@ -64,6 +64,7 @@ struct FrontendParams {
   float* out_log;   int64_t ld_log;
   float* out_diff;  int64_t ld_diff;
   float* out_odf;
+  float* out_lgd;   int64_t ld_lgd;   // |local group delay| / pi (ComplexFlux), N = 2048 only
 };
 
 constexpr int kMaxWarps = 16;

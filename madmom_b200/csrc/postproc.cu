@@ -178,6 +178,58 @@ __global__ void __launch_bounds__(1024) peak_compact_kernel(const PeakParams p) 
   if (threadIdx.x == 0) p.counts[s] = base;
 }
 
+// ---------------------------------------------------------------------------------------------- complex flux
+// One warp per frame.  (1) temporal maximum of |lgd| over `tf` frames (scipy maximum_filter size [tf, 1],
+// origin 0, mode 'reflect' inside the frame's own signal) into a shared row, (2) per band the minimum over the
+// bins [lo, hi) the band touches plus one bin either side, (3) odf = sum_b diff[b] * mask[b].
+// madmom/features/onsets.py:282-317.
+__global__ void __launch_bounds__(256) complex_flux_kernel(const float* __restrict__ lgd, int64_t ld_lgd,
+                                                           const float* __restrict__ diff, int64_t ld_diff,
+                                                           const int32_t* __restrict__ band_lo,
+                                                           const int32_t* __restrict__ band_hi, int32_t n_bands,
+                                                           int32_t n_bins, int64_t rows, int64_t seg_rows,
+                                                           const int64_t* __restrict__ seg, int32_t n_seg, int32_t tf,
+                                                           float* __restrict__ odf) {
+  extern __shared__ float s_rows[];                       // [warps][n_bins]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
+  if (row >= rows) return;
+  int64_t s0 = 0, len = rows;
+  if (seg) {
+    const int s = find_segment(seg, n_seg, row);
+    s0 = seg[s]; len = seg[s + 1] - s0;
+  } else if (seg_rows > 0) {
+    s0 = (row / seg_rows) * seg_rows; len = seg_rows;
+  }
+  const int64_t t = row - s0;
+  float* mx = s_rows + (size_t)warp * n_bins;
+  const int half = tf / 2;
+  for (int k = lane; k < n_bins; k += 32) {
+    float m = lgd[row * ld_lgd + k];
+    for (int j = -half; j <= half; ++j) {
+      if (j == 0 || tf <= 1) continue;
+      int64_t q = t + j;
+      if (q < 0) q = -q - 1;                             // 'reflect': (b a | a b c)
+      if (q >= len) q = 2 * len - q - 1;
+      q = q < 0 ? 0 : (q >= len ? len - 1 : q);
+      m = fmaxf(m, lgd[(s0 + q) * ld_lgd + k]);
+    }
+    mx[k] = m;
+  }
+  __syncwarp();
+  float sum = 0.0f;
+  for (int b = lane; b < n_bands; b += 32) {
+    const int lo = band_lo[b], hi = band_hi[b];
+    float mn = INFINITY;
+    for (int k = lo; k < hi; ++k) mn = fminf(mn, mx[k]);
+    if (hi <= lo) mn = 0.0f;
+    sum += diff[row * ld_diff + b] * mn;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) odf[row] = sum;
+}
+
 }  // namespace
 
 extern "C" MMB_API int mmb_matrix_diff(const float* in_dev, int64_t ld_in, float* out_dev, int64_t ld_out,
@@ -216,5 +268,27 @@ extern "C" MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg
     else peak_flag_kernel<float><<<grid, 256, 0, st>>>(p);
   }
   peak_compact_kernel<<<n_segments, 1024, 0, st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+}
+
+extern "C" MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, const float* diff_dev, int64_t ld_diff,
+                                        const int32_t* band_lo_dev, const int32_t* band_hi_dev, int32_t n_bands,
+                                        int32_t n_bins, int64_t rows, int64_t rows_per_signal,
+                                        const int64_t* seg_offsets_dev, int32_t n_segments, int32_t temporal_filter,
+                                        float* odf_dev, void* stream) {
+  if (!lgd_dev || !diff_dev || !band_lo_dev || !band_hi_dev || !odf_dev || n_bands <= 0 || n_bins <= 0 || rows < 0 ||
+      ld_lgd < n_bins || ld_diff < n_bands || temporal_filter < 0 || (temporal_filter > 1 && temporal_filter % 2 == 0) ||
+      (seg_offsets_dev && n_segments < 1))
+    return MMB_E_INVALID;
+  if (rows == 0) return MMB_OK;
+  const int warps = 8;
+  const size_t smem = (size_t)warps * n_bins * sizeof(float);
+  if (smem > 48 * 1024 &&
+      cudaFuncSetAttribute(complex_flux_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    return MMB_E_CUDA;
+  const int64_t grid = (rows + warps - 1) / warps;
+  complex_flux_kernel<<<(unsigned)grid, warps * 32, smem, (cudaStream_t)stream>>>(
+      lgd_dev, ld_lgd, diff_dev, ld_diff, band_lo_dev, band_hi_dev, n_bands, n_bins, rows, rows_per_signal,
+      seg_offsets_dev, n_segments, temporal_filter, odf_dev);
   return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
 }

@@ -36,10 +36,52 @@ def superflux(spectrogram, diff_frames=None, diff_max_bins=3):
     return diff.flux()
 
 
+class _ComplexFlux(DeviceResult):
+    """ODF of complex_flux: the fused kernel writes |local group delay| / pi per bin and the SuperFlux difference;
+    `mmb_complex_flux` applies the temporal maximum filter, the per-band minimum and the weighted sum."""
+
+    def __init__(self, diff, temporal_filter):
+        DeviceResult.__init__(self, diff._chain.copy())
+        self.diff = diff
+        self.temporal_filter = int(temporal_filter)
+
+    def _shape(self):
+        return (self.diff.shape[0],)
+
+    def _compute(self):
+        import torch
+        from .. import _lib
+        out = self._chain.run(("lgd", "diff"))
+        starts, lens, _ = self.diff.filterbank.band_table()
+        num_bins = self.diff.filterbank.shape[0]
+        lo = np.maximum(starts.astype(np.int64) - 1, 0).astype(np.int32)
+        hi = np.minimum(starts.astype(np.int64) + lens + 1, num_bins).astype(np.int32)
+        dev = out["lgd"].device
+        return _lib.complex_flux(out["lgd"], out["diff"], torch.from_numpy(lo).to(dev), torch.from_numpy(hi).to(dev),
+                                 self.temporal_filter)
+
+
+def complex_flux(spectrogram, diff_frames=None, diff_max_bins=3, temporal_filter=3, temporal_origin=0):
+    """ComplexFlux: SuperFlux weighted by a local-group-delay mask (madmom/features/onsets.py:245-317).
+    The spectrogram must be filtered and its STFT circularly shifted, as in the reference's ComplexFlux program."""
+    spectrogram = _as_spectrogram(spectrogram)
+    if temporal_origin != 0:
+        raise NotImplementedError("temporal_origin != 0 is not available on the GPU path")
+    if temporal_filter > 1 and temporal_filter % 2 == 0:
+        raise NotImplementedError("even temporal_filter sizes are not available on the GPU path")
+    if spectrogram._chain.filterbank is None:
+        raise NotImplementedError("complex_flux of an unfiltered spectrogram is not available on the GPU path")
+    if spectrogram.stft.fft_size != 2048:
+        raise NotImplementedError("complex_flux is implemented for frame_size 2048 only")
+    diff = SpectrogramDifference(spectrogram, diff_frames=diff_frames, diff_max_bins=diff_max_bins,
+                                 positive_diffs=True)
+    return _ComplexFlux(diff, temporal_filter)
+
+
 class SpectralOnsetProcessor(SequentialProcessor):
     """Signal -> frames -> STFT -> spectrogram [-> filterbank] [-> log] -> onset detection function
     (madmom/features/onsets.py:584-683).  The whole chain is one kernel launch."""
-    METHODS = ["superflux", "spectral_flux"]
+    METHODS = ["superflux", "complex_flux", "spectral_flux"]
 
     def __init__(self, onset_method="spectral_flux", **kwargs):
         from ..audio.signal import SignalProcessor, FramedSignalProcessor

@@ -297,3 +297,41 @@ def test_batch_front_end_stack_and_host_path():
     assert r0 == out.shape[0]
     host = fe.run_host(pcm, lens, ("stack",))["stack"].numpy()
     assert np.array_equal(host, out)
+
+
+def test_complex_flux(sig, ref_sample):
+    """bin/ComplexFlux recipe (fps 200, circular shift, d = 2): local group delay rows against the reference's
+    unwrap-based values, ODF within tolerance of the reference and of its shipped fixture, onsets bit-exact.
+    The reference's lgd carries the rounding of a float32 cumulative unwrap (up to 4e-5 on |lgd|/pi); the kernel's
+    values are the exact principal differences, hence the looser bound on the raw lgd rows."""
+    from madmom_b200.audio.filters import LogarithmicFilterbank
+    from madmom_b200.audio.signal import FramedSignal
+    from madmom_b200.audio.stft import ShortTimeFourierTransform
+    from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
+    from madmom_b200.features.onsets import complex_flux, SpectralOnsetProcessor, OnsetPeakPickingProcessor
+    kw = dict(fps=200, filterbank=LogarithmicFilterbank, num_bands=24, fmin=30, fmax=17000, norm_filters=False,
+              log=np.log10, mul=1, add=1, diff_ratio=0.5, diff_max_bins=3, positive_diffs=True)
+    act = SpectralOnsetProcessor(onset_method="complex_flux", **kw)(sig)
+    assert act.shape == (561,)
+    assert_close(np.asarray(act), ref_sample["odf_complexflux_200"], what="complex_flux")
+    assert np.allclose(np.asarray(act), ref_sample["fixture_act_complex_flux"], atol=2e-5)    # tests/test_bin.py:350-386
+    pp = OnsetPeakPickingProcessor(threshold=0.25, pre_max=0.01, post_max=0.05, pre_avg=0.15, post_avg=0,
+                                   combine=0.03, delay=0, fps=200)
+    onsets = pp(act)
+    assert np.array_equal(onsets, ref_sample["onsets_complexflux_200"])
+    assert np.allclose(onsets, ref_sample["fixture_det_complex_flux"], atol=1e-5)
+    # the lgd rows themselves
+    frames = FramedSignal(sig, frame_size=2048, fps=200)
+    spec = LogarithmicFilteredSpectrogram(Spectrogram(ShortTimeFourierTransform(frames, circular_shift=True)),
+                                          num_bands=24, norm_filters=False)
+    cf = complex_flux(spec)
+    lgd = cf._chain.run(("lgd",))["lgd"].cpu().numpy()
+    want = np.abs(ref_sample["lgd_200_rows"]) / np.pi
+    err = np.abs(lgd[ref_sample["rows"]] - want)
+    # bins above ~13 kHz of sample.wav are 70 dB down: their phase is rounding noise of the FP32 / float64 FFTs
+    assert err[:, :600].max() < 1e-4 and np.median(err) < 1e-6 and err.max() < 1e-2
+    assert not lgd[:, -1].any()
+    # tests/test_features_onsets.py:62-86 literal (norm_filters=True, fps 100)
+    spec = LogarithmicFilteredSpectrogram(Spectrogram(FramedSignal(sig), circular_shift=True), num_bands=24)
+    assert np.allclose(complex_flux(spec)[:6], [0, 0.476213485, 0.0877621323, 0.0593151376, 0.0654867291,
+                                                0.0954693183], atol=2e-5)

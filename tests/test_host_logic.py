@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
     assert lib.mmb_version() >= 100
     # struct layouts of the binding match the header (field order / sizes)
     assert ctypes.sizeof(_lib.Track) == 48 and _lib.TRACK_DTYPE.itemsize == 48
-    assert ctypes.sizeof(_lib.Outputs) == 11 * 8
+    assert ctypes.sizeof(_lib.Outputs) == 13 * 8
 
 
 def test_framing_helpers_in_library(ref_framing):

@@ -141,3 +141,42 @@ class BatchFrontEnd(object):
             if o:
                 plan.run_host(pcm, units, o)
         return out
+
+
+def complex_flux_batch(fe, pcm, lengths, temporal_filter=3, scratch_bytes=2 << 30):
+    """ComplexFlux ODF (config 5 of BASELINE.json) for a batch of tracks on the device.  The per-bin local group
+    delay matrix is an intermediate of rows x K floats, so the batch is walked in groups of tracks whose scratch
+    fits `scratch_bytes`; per group: one fused front-end launch (lgd + difference) and one mmb_complex_flux launch.
+    `fe` is a BatchFrontEnd built from a single circular-shift recipe (recipe.COMPLEXFLUX)."""
+    import torch
+    plan = fe.plans[0]
+    if len(fe.plans) != 1:
+        raise ValueError("complex_flux_batch needs a single recipe")
+    pcm = pcm.reshape(-1)
+    T = fe.frame_counts(lengths)
+    offsets = np.concatenate(([0], np.cumsum(lengths)[:-1])).astype(np.int64)
+    rows_total = int(sum(T))
+    dev = pcm.device
+    odf = torch.empty((rows_total,), dtype=torch.float32, device=dev)
+    fb = fe.recipes[0].build_filterbank()
+    starts, lens, _ = fb.band_table()
+    lo = torch.from_numpy(np.maximum(starts.astype(np.int64) - 1, 0).astype(np.int32)).to(dev)
+    hi = torch.from_numpy(np.minimum(starts.astype(np.int64) + lens + 1, fb.shape[0]).astype(np.int32)).to(dev)
+    K, B = plan.num_bins, plan.num_bands
+    max_rows = max(int(scratch_bytes // (4 * (K + B))), max(T) if T else 1)
+    lgd = diff = None
+    i0, row0 = 0, 0
+    while i0 < len(T):
+        i1, rows = i0, 0
+        while i1 < len(T) and (rows + T[i1] <= max_rows or i1 == i0):
+            rows += T[i1]
+            i1 += 1
+        if lgd is None or lgd.shape[0] < rows:
+            lgd = torch.empty((max(rows, 1), K), dtype=torch.float32, device=dev)
+            diff = torch.empty((max(rows, 1), B), dtype=torch.float32, device=dev)
+        units = _lib.make_units(lengths[i0:i1], T[i0:i1], pcm_offsets=offsets[i0:i1])
+        plan.run(pcm, units, {"lgd": lgd[:rows], "diff": diff[:rows]})
+        seg = torch.from_numpy(np.concatenate(([0], np.cumsum(T[i0:i1]))).astype(np.int64)).to(dev)
+        odf[row0:row0 + rows] = _lib.complex_flux(lgd[:rows], diff[:rows], lo, hi, temporal_filter, seg_offsets=seg)
+        i0, row0 = i1, row0 + rows
+    return odf

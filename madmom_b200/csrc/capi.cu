@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -33,6 +34,8 @@ struct mmb_plan {
   int sample_bytes = 2;
   int smem_bytes = 0;
   int warps = 0;
+  int group_warps = 0;
+  mmb::SmemLayout L;
   int ring_rows = 0;
   int chunk_frames = 0;
   int n_passes = 0, max_q = 0, b_pad = 0, w_floats = 0, fb_iters = 0;
@@ -245,16 +248,26 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   }
   // ---- warps per CTA: as many as the shared-memory budget of one SM allows (one persistent CTA per SM)
   const int align_elems = 16 / p->sample_bytes;
+  //      split into groups of `gw` warps that walk their own chunks (their phases drift apart, which keeps the
+  //      FP32 pipes and the shared-memory pipe busy at the same time)
   p->warps = 0;
-  for (int w = mmb::kMaxWarps; w >= 1; --w) {
-    const int fpr = mmb::frames_per_round(N, w);
+  int gw = 16;
+  if (const char* env = std::getenv("MMB_GROUP_WARPS")) gw = std::atoi(env);
+  if (gw != 1 && gw != 2 && gw != 4 && gw != 8 && gw != 16) gw = 16;
+  int wmax = mmb::kMaxWarps;
+  if (const char* env = std::getenv("MMB_WARPS")) wmax = std::min(std::max(std::atoi(env), 1), mmb::kMaxWarps);
+  for (; gw >= 1 && p->warps == 0; gw >>= 1) {
+    const int fpr = mmb::frames_per_round(N, gw);
     const int span = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N + align_elems) + 7) & ~7;
     const int rows = 2 * fpr + cfg->diff_frames;
-    const mmb::SmemLayout L = mmb::smem_layout(N, w, cfg->num_bands, p->n_passes, p->max_q * p->b_pad, p->w_floats, rows, span,
-                                               p->sample_bytes);
-    if (L.total <= (int)prop.sharedMemPerBlockOptin) {
-      p->warps = w; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
-      break;
+    for (int w = wmax / gw * gw; w >= gw; w -= gw) {
+      const mmb::SmemLayout L = mmb::smem_layout(N, w, gw, cfg->num_bands, p->n_passes, p->max_q * p->b_pad,
+                                                 p->w_floats, rows, span, p->sample_bytes);
+      if (L.total <= (int)prop.sharedMemPerBlockOptin) {
+        p->warps = w; p->group_warps = gw; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
+        p->L = L;
+        break;
+      }
     }
   }
   if (p->warps == 0) {
@@ -263,8 +276,10 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   }
   e = mmb::frontend_set_smem(N, p->sample_bytes, (int)prop.sharedMemPerBlockOptin);
   if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)"); }
-  const int fpr = mmb::frames_per_round(N, p->warps);
-  p->chunk_frames = cfg->chunk_frames > 0 ? cfg->chunk_frames : 32 * fpr - cfg->diff_frames;
+  const int fpr = mmb::frames_per_round(N, p->group_warps);
+  int rounds = 32;
+  if (const char* env = std::getenv("MMB_CHUNK_ROUNDS")) rounds = std::max(std::atoi(env), 1);
+  p->chunk_frames = cfg->chunk_frames > 0 ? cfg->chunk_frames : std::max(rounds * fpr - cfg->diff_frames, 1);
   *out = p;
   return MMB_OK;
 }
@@ -273,7 +288,7 @@ extern "C" int mmb_plan_get_info(const mmb_plan* p, mmb_plan_info* info) {
   if (!p || !info) return fail(MMB_E_INVALID, "null argument");
   info->frame_size = p->cfg.frame_size; info->num_bins = p->cfg.frame_size / 2; info->num_bands = p->cfg.num_bands;
   info->chunk_frames = p->chunk_frames; info->smem_bytes = p->smem_bytes; info->ctas_per_sm = 1;
-  info->num_sms = p->num_sms; info->frames_per_round = mmb::frames_per_round(p->cfg.frame_size, p->warps);
+  info->num_sms = p->num_sms; info->frames_per_round = mmb::frames_per_round(p->cfg.frame_size, p->group_warps);
   info->warps = p->warps;
   return MMB_OK;
 }
@@ -357,7 +372,7 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.n_passes = p->n_passes; fp.max_q = p->max_q; fp.b_pad = p->b_pad; fp.w_floats = p->w_floats;
   fp.fb_pass = p->d_pass; fp.fb_w = p->d_fbw; fp.fb_start = p->d_fbstart; fp.fb_pid = p->d_fbpid;
   fp.pcm_extent = pcm_extent; fp.bulk_allowed = ((uintptr_t)pcm_dev % 16) == 0;
-  fp.warps = p->warps; fp.ring_rows = p->ring_rows;
+  fp.warps = p->warps; fp.group_warps = p->group_warps; fp.L = p->L; fp.ring_rows = p->ring_rows;
   fp.mul = p->cfg.mul; fp.add = p->cfg.add; fp.log_mode = p->cfg.log_mode;
   fp.diff_frames = p->cfg.diff_frames; fp.max_bins = p->cfg.diff_max_bins; fp.positive = p->cfg.positive_diffs;
   fp.circular_shift = p->cfg.circular_shift;
@@ -366,8 +381,9 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
   fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;
   fp.out_lgd = o->lgd; fp.ld_lgd = o->ld_lgd;
+  const int groups = p->warps / p->group_warps;
   int grid = p->num_sms;                              // one persistent CTA per SM
-  if (grid > chunks) grid = chunks;
+  if (grid > (chunks + groups - 1) / groups) grid = (chunks + groups - 1) / groups;
   if (grid < 1) return MMB_OK;
   cudaError_t e = mmb::launch_frontend(p->cfg.frame_size, p->sample_bytes, fp, grid, p->smem_bytes, stream);
   if (e != cudaSuccess) return cuda_fail(e, "frontend kernel launch");

@@ -37,6 +37,9 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n"
@@ -56,16 +59,17 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------- round cursor
-// Thread 0 walks the CTA's rounds; `d` is filled for the round that follows (chunk, g0_prev, nfr_prev).
+// One lane walks the rounds of its warp group; `d` is advanced to the round that follows.  Group `vid` of `vstride`
+// groups in the grid takes chunks vid, vid + vstride, ...
 template <int N, typename S>
-__device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, int fpr) {
+__device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, int fpr, int vid, int vstride) {
   const int lead = ((p.out_diff != nullptr) || (p.out_odf != nullptr)) ? p.diff_frames : 0;
   long long g0;
   bool new_chunk = first;
-  int chunk = first ? (int)blockIdx.x : d.chunk;
+  int chunk = first ? vid : d.chunk;
   if (!first) {
     g0 = d.g0 + d.nfr;
-    if (g0 >= d.gb) { chunk += (int)gridDim.x; new_chunk = true; }
+    if (g0 >= d.gb) { chunk += vstride; new_chunk = true; }
   }
   if (new_chunk) {
     if (chunk >= p.total_chunks) { d.nfr = 0; return; }
@@ -102,6 +106,12 @@ __device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, in
   d.shift = d.bulk ? (int)(abs0 - e0) : 0;
 }
 
+// barrier of one warp group (named barrier 1 + group; a single-warp group needs only __syncwarp)
+__device__ __forceinline__ void group_sync(int grp, int gthreads) {
+  if (gthreads == 32) __syncwarp();
+  else asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(gthreads) : "memory");
+}
+
 template <typename S>
 __device__ __forceinline__ void issue_bulk(const FrontendParams& p, const RoundDesc& d, S* buf, uint64_t* bar) {
   constexpr int A = 16 / (int)sizeof(S);
@@ -112,6 +122,27 @@ __device__ __forceinline__ void issue_bulk(const FrontendParams& p, const RoundD
   fence_proxy_async();                            // earlier generic-proxy accesses of buf are ordered before the copy
   mbar_expect_tx(bar, bytes);
   bulk_g2s(buf, reinterpret_cast<const S*>(p.pcm) + e0, bytes, bar);
+}
+
+// Called by every warp of a group once per round, after its last read of the staged span.  The last warp to
+// arrive describes the following round and, when that round can be staged by a bulk copy, starts the copy into the
+// (now idle) span buffer: it lands while the group is busy with the FFTs of the current round.
+template <int N, typename S>
+__device__ __forceinline__ void frames_loaded(const FrontendParams& p, GroupCtl* G, int r, S* buf, int lane, int gw,
+                                              int fpr, int vid, int vstride) {
+  __syncwarp();
+  if (lane == 0) {
+    __threadfence_block();
+    if (atomicAdd(&G->loaded, 1) == gw - 1) {
+      G->loaded = 0;
+      __threadfence_block();
+      RoundDesc* Dn = &G->desc[(r + 1) % 3];
+      *Dn = G->desc[r % 3];
+      next_round<N, S>(p, *Dn, false, fpr, vid, vstride);
+      if (Dn->nfr > 0 && Dn->bulk) issue_bulk<S>(p, *Dn, buf, reinterpret_cast<uint64_t*>(&G->mbar));
+      else mbar_arrive(reinterpret_cast<uint64_t*>(&G->mbar));
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------- per-warp stages
@@ -203,6 +234,21 @@ __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lan
   }
 }
 
+// phase C of one round: max-filter + lagged difference + flux of its frames, coalesced row stores
+__device__ __forceinline__ void round_difference(const FrontendParams& p, const RoundDesc* Dc, const float* s_ring,
+                                                 int gwarp, int GW, int lane, bool want_diff) {
+  const int nb = p.n_bands, R = p.ring_rows, nfr = Dc->nfr, slot0 = Dc->slot0;
+  const long long g0 = Dc->g0, ga = Dc->ga, row0 = Dc->row0;
+  for (int fi = gwarp; fi < nfr; fi += GW) {
+    const long long g = g0 + fi;
+    if (g < ga) continue;                                   // lead-in frame: ring only
+    int sc = slot0 + fi; while (sc >= R) sc -= R;
+    int sp = sc - p.diff_frames; if (sp < 0) sp += R;
+    const bool has_prev = want_diff && (g - p.diff_frames) >= 0;       // first d rows of a signal are zero
+    warp_difference(p, lane, s_ring + sc * nb, s_ring + sp * nb, has_prev, row0 + g);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- the kernel
 template <int N, typename S>
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const FrontendParams p) {
@@ -210,11 +256,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   constexpr int K = N / 2;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nthreads = blockDim.x, warps = nthreads >> 5;
-  const int FPR = frames_per_round(N, warps);
-  const SmemLayout L = smem_layout(N, warps, p.n_bands, p.n_passes, p.max_q * p.b_pad, p.w_floats, p.ring_rows,
-                                   p.span_cap, (int)sizeof(S));
-  uint64_t* s_mbar = reinterpret_cast<uint64_t*>(smem + L.mbar);
-  RoundDesc* s_desc = reinterpret_cast<RoundDesc*>(smem + L.desc);
+  const int GW = p.group_warps, gthreads = GW * 32;
+  const int grp = warp / GW, gwarp = warp - grp * GW, gtid = tid - grp * gthreads;
+  const int vid = (int)blockIdx.x * (warps / GW) + grp, vstride = (int)gridDim.x * (warps / GW);
+  const int FPR = frames_per_round(N, GW);
+  const SmemLayout& L = p.L;
+  GroupCtl* G = reinterpret_cast<GroupCtl*>(smem + L.ctl + grp * L.ctl_stride);
+  uint64_t* g_mbar = reinterpret_cast<uint64_t*>(&G->mbar);
   float* s_win = reinterpret_cast<float*>(smem + L.win);
   float2* s_tw1 = reinterpret_cast<float2*>(smem + L.tw1);
   float2* s_tw2k = reinterpret_cast<float2*>(smem + L.tw2k);
@@ -223,8 +271,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   float* s_w = reinterpret_cast<float*>(smem + L.fb_w);
   int* s_start = reinterpret_cast<int*>(smem + L.fb_start);
   int* s_pid = reinterpret_cast<int*>(smem + L.fb_pid);
-  float* s_ring = reinterpret_cast<float*>(smem + L.ring);
-  const int pcm_stride = mmb_align16(p.span_cap * (int)sizeof(S));
+  float* s_ring = reinterpret_cast<float*>(smem + L.ring + grp * L.ring_stride);
+  S* buf = reinterpret_cast<S*>(smem + L.pcm + grp * L.pcm_stride);
 
   unsigned char* my_scratch = smem + L.scratch + warp * warp_scratch_bytes(N);
   float2* ex = reinterpret_cast<float2*>(my_scratch);
@@ -247,165 +295,177 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     for (int i = tid; i < warps * (L.part_stride / 4); i += nthreads)
       reinterpret_cast<float*>(smem + L.part)[i] = 0.0f;     // part slots without a piece are never written again
   }
-  if (tid == 0) {
-    mbar_init(&s_mbar[0], 1);
-    mbar_init(&s_mbar[1], 1);
+  uint64_t* ring_bar = reinterpret_cast<uint64_t*>(&G->ring_bar);
+  if (gtid == 0) {
+    mbar_init(g_mbar, 1);
+    mbar_init(ring_bar, GW);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    next_round<N, S>(p, s_desc[0], true, FPR);
-    if (s_desc[0].nfr > 0 && s_desc[0].bulk)
-      issue_bulk<S>(p, s_desc[0], reinterpret_cast<S*>(smem + L.pcm), &s_mbar[0]);
+    G->loaded = 0;
+    next_round<N, S>(p, G->desc[0], true, FPR, vid, vstride);
+    if (G->desc[0].nfr > 0 && G->desc[0].bulk) issue_bulk<S>(p, G->desc[0], buf, g_mbar);
+    else mbar_arrive(g_mbar);
   }
   __syncthreads();
 
   const bool want_diff = (p.out_diff != nullptr) || (p.out_odf != nullptr);
   const float sgn_odd = p.circular_shift ? -1.0f : 1.0f;
   const int R = p.ring_rows;
-  uint32_t phase0 = 0, phase1 = 0;          // parity of the next completion of each staging buffer's mbarrier
+  uint32_t pcm_phase = 0, ring_phase = 0;   // parities of the next completions of the group's two mbarriers
   int prev_chunk = -1;
+  bool pending = false;                     // phase C of the previous round is still to be done by this warp
 
-  for (int r = 0;; ++r) {
-    const RoundDesc* D = &s_desc[r % 3];
+  // Phase C of round r-1 is deferred until this warp is about to write its ring row of round r: by then every
+  // warp of the group has long finished its row of round r-1, so the wait costs nothing and the warps are free
+  // to drift apart by up to one round (the ring holds 2 * FPR + d rows).
+#define MMB_PENDING_DIFFERENCE()                                                                       \
+  if (pending) {                                                                                       \
+    mbar_wait(ring_bar, ring_phase);                                                                   \
+    ring_phase ^= 1;                                                                                   \
+    round_difference(p, &G->desc[(r + 2) % 3], s_ring, gwarp, GW, lane, want_diff);                     \
+    pending = false;                                                                                   \
+  }
+#define MMB_ROWS_WRITTEN()                                                                             \
+  {                                                                                                    \
+    __syncwarp();                                                                                      \
+    if (lane == 0) mbar_arrive(ring_bar);                                                              \
+    pending = true;                                                                                    \
+  }
+
+  int r = 0;
+  for (;; ++r) {
+    mbar_wait(g_mbar, pcm_phase);           // descriptor of round r is written, its span staged if `bulk`
+    pcm_phase ^= 1;
+    const RoundDesc* D = &G->desc[r % 3];
     const int nfr = D->nfr;
     if (nfr == 0) break;
-    const int b = r & 1;
-    S* buf = reinterpret_cast<S*>(smem + L.pcm + b * pcm_stride);
-    // a new chunk maps its frames to unrelated ring slots: wait until the slowest warp has finished reading the
-    // previous chunk's rows (within a chunk the ring is large enough for one round of skew)
+    // a new chunk maps its frames to unrelated ring slots: finish the previous chunk first
     if (D->chunk != prev_chunk) {
-      if (r > 0) __syncthreads();
+      MMB_PENDING_DIFFERENCE();
+      if (r > 0) group_sync(grp, gthreads);
       prev_chunk = D->chunk;
     }
-    // ---- thread 0: describe the following round and start its bulk copy into the other buffer (its last
-    //      readers finished before the barrier of the previous round)
-    if (tid == 0) {
-      RoundDesc* Dn = &s_desc[(r + 1) % 3];
-      *Dn = *D;
-      next_round<N, S>(p, *Dn, false, FPR);
-      if (Dn->nfr > 0 && Dn->bulk)
-        issue_bulk<S>(p, *Dn, reinterpret_cast<S*>(smem + L.pcm + (b ^ 1) * pcm_stride), &s_mbar[b ^ 1]);
-    }
-    // ---- this round's PCM span
-    if (D->bulk) {
-      mbar_wait(&s_mbar[b], b ? phase1 : phase0);
-      if (b) phase1 ^= 1; else phase0 ^= 1;
-    } else {
+    // ---- spans that touch the edge of a signal are filled here with zero padding (all warps have read the
+    //      previous span: the descriptor is written by the last of them)
+    if (!D->bulk) {
       const long long l0 = D->l0, plen = D->pcm_len;
       const S* src = reinterpret_cast<const S*>(p.pcm) + D->pcm_offset;
       const int span = D->span;
-      for (int i = tid; i < span; i += nthreads) {
+      for (int i = gtid; i < span; i += gthreads) {
         const long long li = l0 + i;
         S v = (S)0;
         if (li >= 0 && li < plen) v = src[li];
         buf[i] = v;
       }
-      __syncthreads();
+      group_sync(grp, gthreads);
     }
     const long long g0 = D->g0, ga = D->ga, row0 = D->row0, s_begin = D->s_begin;
     const S* span0 = buf + D->shift;
     const int slot0 = D->slot0;
 
-    // ================= phase A+B: this warp's frame(s): FFT -> magnitudes -> filterbank -> ring row
-    {
-      float2 v[32];
-      if (N == 1024) {
-        const int fa = 2 * warp, fb = 2 * warp + 1;
-        if (fa < nfr) {
-          const long long gA = g0 + fa, gB = g0 + fb;
-          const bool haveB = fb < nfr;
-          const S* xa = span0 + (int)(frame_start_sample(gA, p.hop, N, p.origin) - s_begin);
-          const S* xb = haveB ? span0 + (int)(frame_start_sample(gB, p.hop, N, p.origin) - s_begin) : nullptr;
-          load_frames_1024<S>(lane, v, xa, xb, s_win);
-          core_pass1(lane, v, ex, s_tw1);
-          __syncwarp();
-          core_pass2_load(lane, v, ex);
-          __syncwarp();
-          core_pass2_fft(v);
-          core_publish_upper(lane, v, ex, true);
-          __syncwarp();
-          BinSink oa, ob;
-          const long long rowA = row0 + gA, rowB = rowA + 1;
-          oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
-          oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
-          oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
-          ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
-          oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
-          ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
-          if (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row) split_1024x2(lane, v, ex, oa, ob, haveB);
-          else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
-          if (nb > 0) {
-            __syncwarp();
-            if (!haveB) for (int i = lane; i < 512; i += 32) my_mag[512 + i] = 0.0f;
-            __syncwarp();
-            warp_filterbank<2>(p, lane, my_mag, my_mag + 512, my_part, s_pass, s_w, s_start, s_pid);
-            int sa = slot0 + fa; if (sa >= R) sa -= R;
-            warp_band_epilogue(p, lane, my_part, s_ring + sa * nb, rowA, gA >= ga);
-            if (haveB) {
-              int sb = sa + 1; if (sb >= R) sb -= R;
-              warp_band_epilogue(p, lane, my_part + p.max_q * p.b_pad + 1, s_ring + sb * nb, rowB, gB >= ga);
-            }
-          }
-        }
-      } else if (warp < nfr) {
-        const long long g = g0 + warp;
-        const S* x = span0 + (int)(frame_start_sample(g, p.hop, N, p.origin) - s_begin);
-        BinSink o;
-        const long long row = row0 + g;
-        o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
-        o.stft_row = (p.out_stft && g >= ga) ? p.out_stft + row * p.ld_stft : nullptr;
-        o.spec_row = (p.out_spec && g >= ga) ? p.out_spec + row * p.ld_spec : nullptr;
-        if (N == 2048) {
-          load_frame_2048<S>(lane, v, x, s_win);
-          core_pass1(lane, v, ex, s_tw1);
-          __syncwarp();
-          core_pass2_load(lane, v, ex);
-          __syncwarp();
-          core_pass2_fft(v);
-          core_publish_upper(lane, v, ex, true);
-          __syncwarp();
-          if (p.out_lgd && g >= ga) {
-            split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
-          } else if (o.stft_row || o.spec_row) {
-            split_2048(lane, v, ex, s_tw2k, o);
-          } else {
-            split_2048(lane, v, ex, s_tw2k, quiet(o));
-          }
-        } else {
-#pragma unroll 1
-          for (int c = 0; c < 2; ++c) {
-            load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
-            core_pass1(lane, v, ex, s_tw1);
-            __syncwarp();
-            core_pass2_load(lane, v, ex);
-            __syncwarp();
-            core_pass2_fft(v);
-            core_publish_upper(lane, v, ex, c == 0);
-            __syncwarp();
-            if (o.stft_row || o.spec_row) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
-            else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
-            __syncwarp();
-          }
-        }
+    // ================= this warp's frame(s): FFT -> magnitudes -> filterbank -> [phase C of round r-1] -> ring row
+    float2 v[32];
+    if (N == 1024) {
+      const int fa = 2 * gwarp, fb = 2 * gwarp + 1;
+      if (fa >= nfr) {
+        frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+        if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
+      } else {
+        const long long gA = g0 + fa, gB = g0 + fb;
+        const bool haveB = fb < nfr;
+        const S* xa = span0 + (int)(frame_start_sample(gA, p.hop, N, p.origin) - s_begin);
+        const S* xb = haveB ? span0 + (int)(frame_start_sample(gB, p.hop, N, p.origin) - s_begin) : nullptr;
+        load_frames_1024<S>(lane, v, xa, xb, s_win);
+        frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+        core_pass1(lane, v, ex, s_tw1);
+        __syncwarp();
+        core_pass2_load(lane, v, ex);
+        __syncwarp();
+        core_pass2_fft(v);
+        core_publish_upper(lane, v, ex, true);
+        __syncwarp();
+        BinSink oa, ob;
+        const long long rowA = row0 + gA, rowB = rowA + 1;
+        oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
+        oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
+        oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
+        ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
+        oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
+        ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
+        if (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row) split_1024x2(lane, v, ex, oa, ob, haveB);
+        else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
         if (nb > 0) {
           __syncwarp();
-          warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
-          int sl = slot0 + warp; if (sl >= R) sl -= R;
-          warp_band_epilogue(p, lane, my_part, s_ring + sl * nb, row, g >= ga);
+          if (!haveB) for (int i = lane; i < 512; i += 32) my_mag[512 + i] = 0.0f;
+          __syncwarp();
+          warp_filterbank<2>(p, lane, my_mag, my_mag + 512, my_part, s_pass, s_w, s_start, s_pid);
+          MMB_PENDING_DIFFERENCE();
+          int sa = slot0 + fa; if (sa >= R) sa -= R;
+          warp_band_epilogue(p, lane, my_part, s_ring + sa * nb, rowA, gA >= ga);
+          if (haveB) {
+            int sb = sa + 1; if (sb >= R) sb -= R;
+            warp_band_epilogue(p, lane, my_part + p.max_q * p.b_pad + 1, s_ring + sb * nb, rowB, gB >= ga);
+          }
+          MMB_ROWS_WRITTEN();
         }
       }
-    }
-    __syncthreads();          // ring rows of the round are complete; staging buffer b is free again
-    if (nb == 0) continue;
-
-    // ================= phase C: max-filter + lagged difference + flux, coalesced row stores
-    for (int fi = warp; fi < nfr; fi += warps) {
-      const long long g = g0 + fi;
-      if (g < ga) continue;                                   // lead-in frame: ring only
-      int sc = slot0 + fi; while (sc >= R) sc -= R;
-      int sp = sc - p.diff_frames; if (sp < 0) sp += R;
-      const bool has_prev = want_diff && (g - p.diff_frames) >= 0;       // first d rows of a signal are zero
-      warp_difference(p, lane, s_ring + sc * nb, s_ring + sp * nb, has_prev, row0 + g);
+    } else if (gwarp >= nfr) {
+      frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+      if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
+    } else {
+      const long long g = g0 + gwarp;
+      const S* x = span0 + (int)(frame_start_sample(g, p.hop, N, p.origin) - s_begin);
+      BinSink o;
+      const long long row = row0 + g;
+      o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
+      o.stft_row = (p.out_stft && g >= ga) ? p.out_stft + row * p.ld_stft : nullptr;
+      o.spec_row = (p.out_spec && g >= ga) ? p.out_spec + row * p.ld_spec : nullptr;
+      if (N == 2048) {
+        load_frame_2048<S>(lane, v, x, s_win);
+        frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+        core_pass1(lane, v, ex, s_tw1);
+        __syncwarp();
+        core_pass2_load(lane, v, ex);
+        __syncwarp();
+        core_pass2_fft(v);
+        core_publish_upper(lane, v, ex, true);
+        __syncwarp();
+        if (p.out_lgd && g >= ga) {
+          split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
+        } else if (o.stft_row || o.spec_row) {
+          split_2048(lane, v, ex, s_tw2k, o);
+        } else {
+          split_2048(lane, v, ex, s_tw2k, quiet(o));
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
+          if (c == 1) frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+          core_pass1(lane, v, ex, s_tw1);
+          __syncwarp();
+          core_pass2_load(lane, v, ex);
+          __syncwarp();
+          core_pass2_fft(v);
+          core_publish_upper(lane, v, ex, c == 0);
+          __syncwarp();
+          if (o.stft_row || o.spec_row) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
+          else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
+          __syncwarp();
+        }
+      }
+      if (nb > 0) {
+        __syncwarp();
+        warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
+        MMB_PENDING_DIFFERENCE();
+        int sl = slot0 + gwarp; if (sl >= R) sl -= R;
+        warp_band_epilogue(p, lane, my_part, s_ring + sl * nb, row, g >= ga);
+        MMB_ROWS_WRITTEN();
+      }
     }
   }
+  MMB_PENDING_DIFFERENCE();
+#undef MMB_PENDING_DIFFERENCE
+#undef MMB_ROWS_WRITTEN
 }
 
 // ---------------------------------------------------------------------------------------------- host launchers

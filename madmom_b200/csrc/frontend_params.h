@@ -25,6 +25,15 @@ struct FbPass {
   int32_t woff;    // offset (floats) of w[p][0][0] inside the weight table
 };
 
+// byte offsets of the kernel's shared-memory regions (computed once per plan on the host, smem_layout below)
+struct SmemLayout {
+  int ctl, win, tw1, tw2k, tw4k, fb_pass, fb_w, fb_start, fb_pid, ring, scratch, part, pcm, total;
+  int ctl_stride;        // bytes of control block per warp group
+  int ring_stride;       // bytes of log-spectrogram ring per warp group
+  int part_stride;       // bytes of partial sums per warp
+  int pcm_stride;        // bytes of staged PCM span per warp group
+};
+
 struct FrontendParams {
   const void* pcm;               // int16 or float32 samples
   int64_t pcm_extent;            // elements of the PCM buffer that may be read (max over units of offset + len)
@@ -38,6 +47,8 @@ struct FrontendParams {
   int32_t origin;
   int32_t span_cap;              // capacity (samples) of one staged PCM span in shared memory
   int32_t warps;                 // warps per CTA (blockDim.x / 32)
+  int32_t group_warps;           // warps per group; a group walks its own chunks in rounds of frames_per_round frames
+  SmemLayout L;
   // plan constants (device)
   const float* win;              // N floats, fft_window * 0.5
   const float2* tw1;             // 1024: W1024^(l*k1) at [k1*32 + l]
@@ -70,12 +81,12 @@ struct FrontendParams {
 constexpr int kMaxWarps = 16;
 constexpr int kMaxDiffFrames = 16;
 
-// frames one CTA round produces with `warps` warps
-__host__ __device__ constexpr int frames_per_round(int N, int warps) { return N == 1024 ? 2 * warps : warps; }
+// frames one round of a warp group produces
+__host__ __device__ constexpr int frames_per_round(int N, int group_warps) { return N == 1024 ? 2 * group_warps : group_warps; }
 // per-warp scratch (bytes): exchange tile (+ magnitudes aliased in its lower 4 KB; separate 8 KB for 4096)
 __host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? 8448 + 8192 : 8448) + 16; }
 
-// one descriptor per round, written by thread 0, read by everybody (3 slots, see frontend_kernel.cu)
+// one descriptor per round of a group, written by one lane, read by the group (3 slots, see frontend_kernel.cu)
 struct RoundDesc {
   long long g0;          // first (global) frame of the round
   long long ga;          // first output frame of the chunk (frames below are lead-in)
@@ -92,19 +103,25 @@ struct RoundDesc {
   long long gb;          // end of the chunk's output range
 };
 
-struct SmemLayout {
-  int mbar, desc, win, tw1, tw2k, tw4k, fb_pass, fb_w, fb_start, fb_pid, ring, scratch, part, pcm, total;
-  int part_stride;       // bytes of partial sums per warp
+// control block of one warp group
+struct GroupCtl {
+  RoundDesc desc[3];
+  unsigned long long mbar;   // phase r completes when the descriptor of round r is written and its PCM span staged
+  unsigned long long ring_bar;   // phase r completes when every warp of the group has written its ring rows of round r
+  int loaded;                // warps of the group that have read their frames of the current round
+  int pad;
 };
 
 __host__ __device__ inline int mmb_align16(int x) { return (x + 15) & ~15; }
 
-__host__ __device__ inline SmemLayout smem_layout(int N, int warps, int n_bands, int n_passes, int part_floats,
-                                                  int w_floats, int ring_rows, int span_cap, int sample_bytes) {
+// `ring_rows`, `span_cap` are per group
+inline SmemLayout smem_layout(int N, int warps, int group_warps, int n_bands, int n_passes, int part_floats,
+                              int w_floats, int ring_rows, int span_cap, int sample_bytes) {
   SmemLayout L;
+  const int groups = warps / group_warps;
   int o = 0;
-  L.mbar = o;        o += 16;
-  L.desc = o;        o += mmb_align16(3 * (int)sizeof(RoundDesc));
+  L.ctl_stride = mmb_align16((int)sizeof(GroupCtl));
+  L.ctl = o;         o += groups * L.ctl_stride;
   L.win = o;         o += mmb_align16(N * 4);
   L.tw1 = o;         o += 1024 * 8;
   L.tw2k = o;        o += (N == 1024 ? 0 : (N == 2048 ? 512 * 8 : 1024 * 8));
@@ -113,11 +130,13 @@ __host__ __device__ inline SmemLayout smem_layout(int N, int warps, int n_bands,
   L.fb_w = o;        o += mmb_align16(w_floats * 4);
   L.fb_start = o;    o += mmb_align16(n_passes * 32 * 4);
   L.fb_pid = o;      o += mmb_align16(n_passes * 32 * 4);
-  L.ring = o;        o += mmb_align16(n_bands > 0 ? ring_rows * n_bands * 4 : 0);
+  L.ring_stride = mmb_align16(n_bands > 0 ? ring_rows * n_bands * 4 : 0);
+  L.ring = o;        o += groups * L.ring_stride;
   L.scratch = o;     o += warps * warp_scratch_bytes(N);
   L.part_stride = mmb_align16((part_floats + 1) * 4 * (N == 1024 ? 2 : 1));
   L.part = o;        o += n_bands > 0 ? warps * L.part_stride : 0;
-  L.pcm = o;         o += 2 * mmb_align16(span_cap * sample_bytes);
+  L.pcm_stride = mmb_align16(span_cap * sample_bytes);
+  L.pcm = o;         o += groups * L.pcm_stride;
   L.total = o;
   return L;
 }

@@ -251,23 +251,21 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   //      split into groups of `gw` warps that walk their own chunks (their phases drift apart, which keeps the
   //      FP32 pipes and the shared-memory pipe busy at the same time)
   p->warps = 0;
-  int gw = 16;
-  if (const char* env = std::getenv("MMB_GROUP_WARPS")) gw = std::atoi(env);
-  if (gw != 1 && gw != 2 && gw != 4 && gw != 8 && gw != 16) gw = 16;
+  int gw_req = 0;                                           // 0: one group of all warps
+  if (const char* env = std::getenv("MMB_GROUP_WARPS")) gw_req = std::max(std::atoi(env), 0);
   int wmax = mmb::kMaxWarps;
   if (const char* env = std::getenv("MMB_WARPS")) wmax = std::min(std::max(std::atoi(env), 1), mmb::kMaxWarps);
-  for (; gw >= 1 && p->warps == 0; gw >>= 1) {
+  for (int w = wmax; w >= 1 && p->warps == 0; --w) {
+    const int gw = (gw_req > 0 && gw_req <= w) ? gw_req : w;
+    if (w % gw != 0 || (w / gw > 15 && gw > 1)) continue;      // named barriers 1 .. 15, one per group
     const int fpr = mmb::frames_per_round(N, gw);
     const int span = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N + align_elems) + 7) & ~7;
     const int rows = 2 * fpr + cfg->diff_frames;
-    for (int w = wmax / gw * gw; w >= gw; w -= gw) {
-      const mmb::SmemLayout L = mmb::smem_layout(N, w, gw, cfg->num_bands, p->n_passes, p->max_q * p->b_pad,
-                                                 p->w_floats, rows, span, p->sample_bytes);
-      if (L.total <= (int)prop.sharedMemPerBlockOptin) {
-        p->warps = w; p->group_warps = gw; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
-        p->L = L;
-        break;
-      }
+    const mmb::SmemLayout L = mmb::smem_layout(N, w, gw, cfg->num_bands, p->n_passes, p->max_q * p->b_pad,
+                                               p->w_floats, rows, span, p->sample_bytes);
+    if (L.total <= (int)prop.sharedMemPerBlockOptin) {
+      p->warps = w; p->group_warps = gw; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
+      p->L = L;
     }
   }
   if (p->warps == 0) {

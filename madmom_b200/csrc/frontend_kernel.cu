@@ -46,9 +46,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       ".reg .pred P1;\n"
       "WAIT_LOOP:\n"
       "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-      "@P1 bra DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "DONE:\n"
+      "@!P1 bra WAIT_LOOP;\n"
       "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 // global -> shared bulk copy (UBLKCP); dst, src 16-byte aligned, bytes a multiple of 16
@@ -126,7 +124,8 @@ __device__ __forceinline__ void issue_bulk(const FrontendParams& p, const RoundD
 
 // Called by every warp of a group once per round, after its last read of the staged span.  The last warp to
 // arrive describes the following round and, when that round can be staged by a bulk copy, starts the copy into the
-// (now idle) span buffer: it lands while the group is busy with the FFTs of the current round.
+// (now idle) span buffer: it lands while the group is busy with the FFTs of the current round.  Otherwise it just
+// completes the barrier phase and the threads fill the span at the start of the round.
 template <int N, typename S>
 __device__ __forceinline__ void frames_loaded(const FrontendParams& p, GroupCtl* G, int r, S* buf, int lane, int gw,
                                               int fpr, int vid, int vstride) {
@@ -136,8 +135,8 @@ __device__ __forceinline__ void frames_loaded(const FrontendParams& p, GroupCtl*
     if (atomicAdd(&G->loaded, 1) == gw - 1) {
       G->loaded = 0;
       __threadfence_block();
-      RoundDesc* Dn = &G->desc[(r + 1) % 3];
-      *Dn = G->desc[r % 3];
+      RoundDesc* Dn = &G->desc[(r + 1) & 3];
+      *Dn = G->desc[r & 3];
       next_round<N, S>(p, *Dn, false, fpr, vid, vstride);
       if (Dn->nfr > 0 && Dn->bulk) issue_bulk<S>(p, *Dn, buf, reinterpret_cast<uint64_t*>(&G->mbar));
       else mbar_arrive(reinterpret_cast<uint64_t*>(&G->mbar));
@@ -162,22 +161,22 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
     const float* w = s_w + fp.woff + lane;
     const float* m0 = mag0 + st;
     const float* m1 = (NF == 2) ? mag1 + st : mag0;
-    float a0 = 0.0f, a1 = 0.0f;
+    float a0 = 0.0f, a1 = 0.0f, c0 = 0.0f, c1 = 0.0f;    // even / odd taps, two frames
 #pragma unroll 1
     for (int i = 0; i < fp.iters; i += 4) {          // pass lengths are multiples of four (capi.cu)
       const float w0 = w[0], w1 = w[32], w2 = w[64], w3 = w[96];
       const float x0 = m0[0], x1 = m0[1], x2 = m0[2], x3 = m0[3];
-      a0 = fmaf(x0, w0, a0); a0 = fmaf(x1, w1, a0); a0 = fmaf(x2, w2, a0); a0 = fmaf(x3, w3, a0);
+      a0 = fmaf(x0, w0, a0); c0 = fmaf(x1, w1, c0); a0 = fmaf(x2, w2, a0); c0 = fmaf(x3, w3, c0);
       if (NF == 2) {
         const float y0 = m1[0], y1 = m1[1], y2 = m1[2], y3 = m1[3];
-        a1 = fmaf(y0, w0, a1); a1 = fmaf(y1, w1, a1); a1 = fmaf(y2, w2, a1); a1 = fmaf(y3, w3, a1);
+        a1 = fmaf(y0, w0, a1); c1 = fmaf(y1, w1, c1); a1 = fmaf(y2, w2, a1); c1 = fmaf(y3, w3, c1);
         m1 += 4;
       }
       w += 128; m0 += 4;
     }
     const int pid = s_pid[ps * 32 + lane];
-    part[pid] = a0;
-    if (NF == 2) part[np1 + pid] = a1;
+    part[pid] = a0 + c0;
+    if (NF == 2) part[np1 + pid] = a1 + c1;
   }
   __syncwarp();
 }
@@ -301,6 +300,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     mbar_init(ring_bar, GW);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     G->loaded = 0;
+    G->described = 0;
     next_round<N, S>(p, G->desc[0], true, FPR, vid, vstride);
     if (G->desc[0].nfr > 0 && G->desc[0].bulk) issue_bulk<S>(p, G->desc[0], buf, g_mbar);
     else mbar_arrive(g_mbar);
@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   if (pending) {                                                                                       \
     mbar_wait(ring_bar, ring_phase);                                                                   \
     ring_phase ^= 1;                                                                                   \
-    round_difference(p, &G->desc[(r + 2) % 3], s_ring, gwarp, GW, lane, want_diff);                     \
+    round_difference(p, &G->desc[(r + 3) & 3], s_ring, gwarp, GW, lane, want_diff);                     \
     pending = false;                                                                                   \
   }
 #define MMB_ROWS_WRITTEN()                                                                             \
@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   for (;; ++r) {
     mbar_wait(g_mbar, pcm_phase);           // descriptor of round r is written, its span staged if `bulk`
     pcm_phase ^= 1;
-    const RoundDesc* D = &G->desc[r % 3];
+    const RoundDesc* D = &G->desc[r & 3];
     const int nfr = D->nfr;
     if (nfr == 0) break;
     // a new chunk maps its frames to unrelated ring slots: finish the previous chunk first

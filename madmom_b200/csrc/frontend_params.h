@@ -86,7 +86,7 @@ __host__ __device__ constexpr int frames_per_round(int N, int group_warps) { ret
 // per-warp scratch (bytes): exchange tile (+ magnitudes aliased in its lower 4 KB; separate 8 KB for 4096)
 __host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? 8448 + 8192 : 8448) + 16; }
 
-// one descriptor per round of a group, written by one lane, read by the group (3 slots, see frontend_kernel.cu)
+// one descriptor per round of a group, written by one lane, read by the group (4 slots, see frontend_kernel.cu)
 struct RoundDesc {
   long long g0;          // first (global) frame of the round
   long long ga;          // first output frame of the chunk (frames below are lead-in)
@@ -105,11 +105,11 @@ struct RoundDesc {
 
 // control block of one warp group
 struct GroupCtl {
-  RoundDesc desc[3];
+  RoundDesc desc[4];         // rounds r-1 (its phase C may be pending), r, r+1 (being written) live at the same time
   unsigned long long mbar;   // phase r completes when the descriptor of round r is written and its PCM span staged
   unsigned long long ring_bar;   // phase r completes when every warp of the group has written its ring rows of round r
   int loaded;                // warps of the group that have read their frames of the current round
-  int pad;
+  int described;             // last round whose descriptor is complete
 };
 
 __host__ __device__ inline int mmb_align16(int x) { return (x + 15) & ~15; }

@@ -5,7 +5,7 @@ from madmom_b200.batch import BatchFrontEnd
 from madmom_b200.synth import make_batch_torch
 pcm = make_batch_torch(1024, 30.0, device='cuda', seed=1)
 lengths = [pcm.shape[1]] * 1024
-for gw in (16, 4, 2):
+for gw in (0,):
     for wmax in (16,):
         if wmax % gw: continue
         os.environ['MMB_GROUP_WARPS'] = str(gw); os.environ['MMB_WARPS'] = str(wmax)

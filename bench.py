@@ -298,7 +298,9 @@ def run_ours(args):
     if os.path.exists(tp):
         try:
             with open(tp) as f:
-                traffic = json.load(f).get(args.workload)
+                t = json.load(f).get(args.workload)
+            # measured DRAM bytes per frame (ncu --set full of the same command) x frames of one launch
+            traffic = float(t["dram_bytes_per_frame"]) * frames_per_step / len(recipes) if t else None
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,

@@ -68,16 +68,17 @@ def main():
                     return float(d[k].replace(",", ""))
                 except Exception:
                     return float("nan")
+            def nbytes(k):
+                return num(k) * {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1, "Tbyte": 1e12}.get(u.get(k), 1)
             un = u.get("gpu__time_duration.sum", "ns")
             t = num("gpu__time_duration.sum") * {"ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}.get(un, 1e-9)
             print("  per frame (%.0f frames/launch): %.1f warp-instructions, %.1f shared wavefronts, %.1f DRAM bytes, "
                   "%.1f SM-cycles/frame/SM" % (frames, num("smsp__inst_executed.sum") / frames,
                                                 num("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum") / frames,
-                                                (num("dram__bytes_read.sum") + num("dram__bytes_write.sum")) *
-                                                {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1}.get(
-                                                    u.get("dram__bytes_read.sum"), 1) / frames,
+                                                (nbytes("dram__bytes_read.sum") + nbytes("dram__bytes_write.sum")) / frames,
                                                 num("sm__cycles_elapsed.avg") * 148 / frames))
             print("  duration %.3f ms" % (t * 1e3))
+            print("  dram traffic per launch: %.0f bytes" % (nbytes("dram__bytes_read.sum") + nbytes("dram__bytes_write.sum")))
 
 
 if __name__ == "__main__":

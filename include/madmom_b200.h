@@ -165,6 +165,41 @@ MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, const float* 
                              int64_t rows, int64_t rows_per_signal, const int64_t* seg_offsets_dev, int32_t n_segments,
                              int32_t temporal_filter, float* odf_dev, void* stream);
 
+/* PCM ingest (madmom/audio/signal.py:170-223 `remix`, called from Signal.__new__ :600-632): interleaved
+ * (num_frames, num_channels) int16 (sample_bytes 2) or float32 (4) on the device -> mono of the same type.
+ * channel = -1: mean over the channels with the reference's rounding (np.mean(..., axis=-1).astype(dtype): integer
+ * samples truncate towards zero); channel >= 0: that channel verbatim. */
+MMB_API int mmb_remix_mono(const void* in_dev, int32_t sample_bytes, int64_t num_frames, int32_t num_channels,
+                           int32_t channel, void* out_dev, void* stream);
+
+/* mmb_run_host for interleaved multi-channel host PCM: unit offsets / lengths count sample FRAMES; each group is
+ * copied to the device interleaved and mixed down there (mmb_remix_mono) before the front end runs. */
+MMB_API int mmb_run_host_interleaved(const mmb_plan* plan, const mmb_track* units, int32_t n, const void* pcm_host,
+                                     int32_t num_channels, int32_t channel, const mmb_outputs* outs_host,
+                                     int32_t* launches);
+
+/* The other spectral onset detection functions of madmom/features/onsets.py, one value per row:
+ *   HFC                      high_frequency_content   :102-127   mean_k spec[t,k] * k
+ *   SPECTRAL_DIFF            spectral_diff            :130-160   sum_k max(spec[t,k] - spec[t-d,k], 0)^2
+ *   MKL                      modified_kullback_leibler :320-362  mean_k log(1 + spec[t,k] / (spec[t-d,k] + eps))
+ *   PHASE_DEV                phase_deviation          :390-414   mean_k |wrap(phi[t] - 2 phi[t-1] + phi[t-2])|
+ *   WEIGHTED_PHASE_DEV       weighted_phase_deviation :417-446   mean_k |wrap(..) * |X[t,k]||
+ *   NORM_WEIGHTED_PHASE_DEV  normalized_weighted_...  :449-479   the above / (mean_k |X[t,k]| + eps)
+ *   COMPLEX_DOMAIN           complex_domain           :482-549   sum_k |X[t,k] - |X[t-1,k]| e^{i(2 phi[t-1] - phi[t-2])}|
+ *   RECTIFIED_COMPLEX_DOMAIN rectified_complex_domain :552-581   the same over bins whose magnitude rose against t-d
+ * The first three read a magnitude matrix `spec_dev` (any spectrogram: raw, filtered, logarithmic), the others the
+ * complex64 STFT `stft_dev` (re, im pairs).  Rows before the start of a signal count as zero rows of the lagged
+ * terms, as in the reference.  Signals: see mmb_complex_flux. */
+enum {
+  MMB_ODF_HFC = 1, MMB_ODF_SPECTRAL_DIFF = 2, MMB_ODF_MKL = 3, MMB_ODF_PHASE_DEV = 4,
+  MMB_ODF_WEIGHTED_PHASE_DEV = 5, MMB_ODF_NORM_WEIGHTED_PHASE_DEV = 6, MMB_ODF_COMPLEX_DOMAIN = 7,
+  MMB_ODF_RECTIFIED_COMPLEX_DOMAIN = 8
+};
+MMB_API int mmb_spectral_odf(int32_t mode, const void* stft_dev, int64_t ld_stft, const float* spec_dev,
+                             int64_t ld_spec, int64_t rows, int32_t cols, int64_t rows_per_signal,
+                             const int64_t* seg_offsets_dev, int32_t n_segments, int32_t diff_frames, double epsilon,
+                             float* odf_dev, void* stream);
+
 /* Calibration: measured FP32 FMA throughput of `device` in TFLOP/s (dependent FFMA chains on every SM,
  * best of 5, CUDA events).  The front end is FP32-pipe bound; bench.py reports its roofline against this. */
 MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops);

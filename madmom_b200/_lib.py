@@ -57,12 +57,17 @@ EXPORTS = {
     "mmb_layout_destroy": (c_i32, [c_vp]),
     "mmb_run": (c_i32, [c_vp, c_vp, c_vp, ctypes.POINTER(Outputs), c_vp, ctypes.POINTER(c_i32)]),
     "mmb_run_host": (c_i32, [c_vp, c_vp, c_i32, c_vp, ctypes.POINTER(Outputs), ctypes.POINTER(c_i32)]),
+    "mmb_run_host_interleaved": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_i32, c_i32, ctypes.POINTER(Outputs),
+                                         ctypes.POINTER(c_i32)]),
+    "mmb_remix_mono": (c_i32, [c_vp, c_i32, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "mmb_host_alloc": (c_i32, [ctypes.POINTER(c_vp), c_i64]),
     "mmb_host_free": (c_i32, [c_vp]),
     "mmb_measure_fp32_peak": (c_i32, [c_i32, ctypes.POINTER(c_f64)]),
     "mmb_rate_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
     "mmb_matrix_diff": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i32, c_i64, c_i32, c_i32, c_i32, c_vp]),
     "mmb_complex_flux": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_i32, c_i32, c_i64, c_i64, c_vp, c_i32, c_i32,
+                                 c_vp, c_vp]),
+    "mmb_spectral_odf": (c_i32, [c_i32, c_vp, c_i64, c_vp, c_i64, c_i64, c_i32, c_i64, c_vp, c_i32, c_i32, c_f64,
                                  c_vp, c_vp]),
     "mmb_peak_picking": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp,
                                  c_vp, c_vp]),
@@ -275,9 +280,11 @@ class FrontEndPlan(object):
         launch_count += n.value
         return n.value
 
-    def run_host(self, pcm, units, outputs):
+    def run_host(self, pcm, units, outputs, num_channels=1, channel=None):
         """Host path (mmb_run_host).  pcm: contiguous numpy array or CPU tensor; outputs: {name: numpy array
-        or CPU tensor}; returns when the outputs are complete."""
+        or CPU tensor}; returns when the outputs are complete.  num_channels > 1: `pcm` holds interleaved sample
+        frames (unit offsets / lengths count frames) and is mixed down on the device (`channel` None: mean over the
+        channels as madmom.audio.signal.remix does, else that channel)."""
         global launch_count
         units = np.ascontiguousarray(units, dtype=TRACK_DTYPE)
 
@@ -291,8 +298,14 @@ class FrontEndPlan(object):
         ptrs = {name: (addr(a), strides(a)) for name, a in outputs.items()}
         o = self._fill(outputs, ptrs)
         n = c_i32(0)
-        _check(self._lib.mmb_run_host(self._handle, units.ctypes.data_as(c_vp), len(units), addr(pcm),
-                                      ctypes.byref(o), ctypes.byref(n)))
+        if num_channels == 1:
+            _check(self._lib.mmb_run_host(self._handle, units.ctypes.data_as(c_vp), len(units), addr(pcm),
+                                          ctypes.byref(o), ctypes.byref(n)))
+        else:
+            _check(self._lib.mmb_run_host_interleaved(self._handle, units.ctypes.data_as(c_vp), len(units),
+                                                      addr(pcm), int(num_channels),
+                                                      -1 if channel is None else int(channel), ctypes.byref(o),
+                                                      ctypes.byref(n)))
         launch_count += n.value
         return n.value
 
@@ -363,3 +376,50 @@ def complex_flux(lgd, diff, band_lo, band_hi, temporal_filter=3, rows_per_signal
         raise ValueError("mmb_complex_flux: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_complex_flux failed")
     launch_count += 1 if rows else 0
     return odf
+
+
+ODF_MODES = {"high_frequency_content": 1, "spectral_diff": 2, "modified_kullback_leibler": 3, "phase_deviation": 4,
+             "weighted_phase_deviation": 5, "normalized_weighted_phase_deviation": 6, "complex_domain": 7,
+             "rectified_complex_domain": 8}
+
+
+def spectral_odf(mode, stft=None, spec=None, diff_frames=1, epsilon=2.220446049250313e-16, rows_per_signal=0,
+                 seg_offsets=None):
+    """mmb_spectral_odf: `mode` a key of ODF_MODES; `spec` (rows, cols) float32 or `stft` (rows, K) complex64 CUDA
+    tensor (row stride arbitrary, columns contiguous).  Returns the (rows,) float32 function on the device."""
+    global launch_count
+    import torch
+    m = ODF_MODES[mode]
+    src = spec if m <= 3 else stft
+    if src is None or src.dim() != 2 or src.stride(1) != 1:
+        raise ValueError("%s needs a 2-D %s tensor with contiguous columns" % (mode, "spec" if m <= 3 else "stft"))
+    want = torch.float32 if m <= 3 else torch.complex64
+    if src.dtype != want or not src.is_cuda:
+        raise ValueError("%s needs a CUDA tensor of dtype %s" % (mode, want))
+    rows, cols = src.shape
+    odf = torch.empty((rows,), dtype=torch.float32, device=src.device)
+    n_seg = 0 if seg_offsets is None else int(seg_offsets.shape[0]) - 1
+    rc = load().mmb_spectral_odf(m, src.data_ptr() if m > 3 else None, src.stride(0) if m > 3 else 0,
+                                 src.data_ptr() if m <= 3 else None, src.stride(0) if m <= 3 else 0, rows, cols,
+                                 int(rows_per_signal), None if seg_offsets is None else seg_offsets.data_ptr(), n_seg,
+                                 int(diff_frames), float(epsilon), odf.data_ptr(), _stream(src.device.index))
+    if rc != MMB_OK:
+        raise ValueError("mmb_spectral_odf: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_spectral_odf failed")
+    launch_count += 1 if rows else 0
+    return odf
+
+
+def remix_mono(pcm, channel=None):
+    """mmb_remix_mono: (num_frames, num_channels) int16 / float32 CUDA tensor -> (num_frames,) mono tensor of the
+    same dtype (mean over the channels with the reference's rounding, or one channel)."""
+    global launch_count
+    import torch
+    if not pcm.is_cuda or pcm.dim() != 2 or not pcm.is_contiguous() or pcm.dtype not in (torch.int16, torch.float32):
+        raise ValueError("pcm must be a contiguous (num_frames, num_channels) int16 or float32 CUDA tensor")
+    n, c = pcm.shape
+    out = torch.empty((n,), dtype=pcm.dtype, device=pcm.device)
+    rc = load().mmb_remix_mono(pcm.data_ptr(), pcm.element_size(), n, c, -1 if channel is None else int(channel),
+                               out.data_ptr(), _stream(pcm.device.index))
+    _check(rc)
+    launch_count += 1 if n else 0
+    return out

@@ -121,13 +121,21 @@ class BatchFrontEnd(object):
         return out
 
     # ------------------------------------------------------------------------------------------ host
-    def run_host(self, pcm, lengths=None, outputs=("diff",), out=None):
+    def run_host(self, pcm, lengths=None, outputs=("diff",), out=None, num_channels=1, channel=None):
         """pcm: host array / CPU tensor (pinned for full speed).  Outputs are host tensors (pinned when
-        allocated here).  Returns when they are complete."""
+        allocated here).  Returns when they are complete.  num_channels > 1: the last axis of `pcm` holds the
+        interleaved channels ((tracks, samples, channels) or (total_samples, channels)); `lengths` count sample
+        frames and the mix-down to mono (madmom.audio.signal.remix) happens on the device."""
         import torch
         if isinstance(pcm, np.ndarray):
             pcm = torch.from_numpy(pcm)
-        if pcm.dim() == 2 and lengths is None:
+        if num_channels > 1:
+            if pcm.shape[-1] != num_channels:
+                raise ValueError("last axis of pcm must hold the %d channels" % num_channels)
+            pcm = pcm.reshape(pcm.shape[:-1].numel(), num_channels) if pcm.dim() != 3 else pcm
+            if pcm.dim() == 3 and lengths is None:
+                lengths = [pcm.shape[1]] * pcm.shape[0]
+        elif pcm.dim() == 2 and lengths is None:
             lengths = [pcm.shape[1]] * pcm.shape[0]
         pcm = pcm.reshape(-1)
         units, T = self.units(lengths)
@@ -139,7 +147,7 @@ class BatchFrontEnd(object):
             out = self._alloc(outputs, rows, make)
         for plan, o in zip(self.plans, self._per_plan_outputs(out)):
             if o:
-                plan.run_host(pcm, units, o)
+                plan.run_host(pcm, units, o, num_channels=num_channels, channel=channel)
         return out
 
 

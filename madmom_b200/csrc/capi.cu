@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -26,7 +27,43 @@ static int cuda_fail(cudaError_t e, const char* what) {
 }
 #define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
 
+namespace {
+// One stage of the host pipeline of mmb_run_host: its own stream and device buffers, reused from call to call.
+struct Slot {
+  cudaStream_t stream = nullptr;
+  void* d_pcm = nullptr; size_t pcm_cap = 0;
+  void* d_raw = nullptr; size_t raw_cap = 0;     // interleaved multi-channel PCM before the down-mix
+  void* d_out[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; size_t out_cap[7] = {0, 0, 0, 0, 0, 0, 0};
+  Track* d_tracks = nullptr; size_t tracks_cap = 0;
+  int32_t* d_prefix = nullptr; size_t prefix_cap = 0;
+};
+
+static cudaError_t ensure(void** p, size_t* cap, size_t need) {
+  if (need <= *cap) return cudaSuccess;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  cudaError_t e = cudaMalloc(p, need);
+  if (e == cudaSuccess) *cap = need;
+  return e;
+}
+
+struct HostPipe {
+  std::mutex mu;
+  Slot slots[3];
+};
+
+void free_slots(Slot* slots, int n) {
+  for (int s = 0; s < n; ++s) {
+    if (slots[s].stream) { cudaStreamSynchronize(slots[s].stream); cudaStreamDestroy(slots[s].stream); }
+    cudaFree(slots[s].d_pcm); cudaFree(slots[s].d_raw); cudaFree(slots[s].d_tracks); cudaFree(slots[s].d_prefix);
+    for (int k = 0; k < 7; ++k) cudaFree(slots[s].d_out[k]);
+    slots[s] = Slot();
+  }
+}
+}  // namespace
+
 struct mmb_plan {
+  HostPipe* pipe = nullptr;      // buffers of mmb_run_host, kept between calls
   mmb_config cfg;
   int num_sms = 0;
   int nnz = 0;
@@ -81,6 +118,7 @@ extern "C" int mmb_plan_destroy(mmb_plan* p) {
   if (!p) return MMB_OK;
   cudaFree(p->d_win); cudaFree(p->d_tw1); cudaFree(p->d_tw2k); cudaFree(p->d_tw4k);
   cudaFree(p->d_pass); cudaFree(p->d_fbw); cudaFree(p->d_fbstart); cudaFree(p->d_fbpid);
+  if (p->pipe) { free_slots(p->pipe->slots, 3); delete p->pipe; }
   delete p;
   return MMB_OK;
 }
@@ -206,6 +244,8 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   }
   mmb_plan* p = new (std::nothrow) mmb_plan();
   if (!p) return fail(MMB_E_NOMEM, "out of host memory");
+  p->pipe = new (std::nothrow) HostPipe();
+  if (!p->pipe) { delete p; return fail(MMB_E_NOMEM, "out of host memory"); }
   p->cfg = *cfg;
   p->cfg.fft_window = nullptr; p->cfg.band_start = nullptr; p->cfg.band_len = nullptr; p->cfg.band_weights = nullptr;
   p->nnz = nnz;
@@ -418,28 +458,13 @@ namespace {
 constexpr int kSlots = 3;
 constexpr int64_t kGroupBytes = 64ll << 20;
 
-struct Slot {
-  cudaStream_t stream = nullptr;
-  void* d_pcm = nullptr; size_t pcm_cap = 0;
-  void* d_out[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; size_t out_cap[7] = {0, 0, 0, 0, 0, 0, 0};
-  Track* d_tracks = nullptr; size_t tracks_cap = 0;
-  int32_t* d_prefix = nullptr; size_t prefix_cap = 0;
-};
-
-static cudaError_t ensure(void** p, size_t* cap, size_t need) {
-  if (need <= *cap) return cudaSuccess;
-  if (*p) cudaFree(*p);
-  *p = nullptr; *cap = 0;
-  cudaError_t e = cudaMalloc(p, need);
-  if (e == cudaSuccess) *cap = need;
-  return e;
-}
 }  // namespace
 
-extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n, const void* pcm_host,
-                            const mmb_outputs* oh, int32_t* launches) {
+static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, const void* pcm_host,
+                         int32_t channels, int32_t channel, const mmb_outputs* oh, int32_t* launches) {
   if (launches) *launches = 0;
   if (!p || !pcm_host) return fail(MMB_E_INVALID, "null argument");
+  if (channels < 1 || channel < -1 || channel >= channels) return fail(MMB_E_INVALID, "bad channel count / index");
   int rc = validate_units(units, n);
   if (rc) return rc;
   rc = check_outputs(p, oh);
@@ -458,15 +483,17 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
   for (int k = 0; k < 7; ++k)
     if (hptr[k] && hld[k] < width[k]) return fail(MMB_E_INVALID, "leading dimension smaller than the row width");
 
-  Slot slots[kSlots];
+  // the plan's own pipeline buffers when no other thread is using them, else temporary ones
+  Slot local[kSlots];
+  std::unique_lock<std::mutex> lock(p->pipe->mu, std::try_to_lock);
+  Slot* slots = lock.owns_lock() ? p->pipe->slots : local;
   int used_slots = 0, n_launch = 0;
   int status = MMB_OK;
   auto cleanup = [&]() {
-    for (int s = 0; s < kSlots; ++s) {
-      if (slots[s].stream) { cudaStreamSynchronize(slots[s].stream); cudaStreamDestroy(slots[s].stream); }
-      cudaFree(slots[s].d_pcm); cudaFree(slots[s].d_tracks); cudaFree(slots[s].d_prefix);
-      for (int k = 0; k < 7; ++k) cudaFree(slots[s].d_out[k]);
-    }
+    if (slots == local) free_slots(local, kSlots);
+    else
+      for (int s = 0; s < kSlots; ++s)
+        if (slots[s].stream) cudaStreamSynchronize(slots[s].stream);
   };
 #define CUS(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { status = cuda_fail(e_, #x); goto done; } } while (0)
   {
@@ -520,8 +547,20 @@ extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n
       od.lgd = hptr[6] ? (float*)S.d_out[6] : nullptr; od.ld_lgd = K;
       CUS(cudaMemcpyAsync(S.d_tracks, tab.data(), tab.size() * sizeof(Track), cudaMemcpyHostToDevice, S.stream));
       CUS(cudaMemcpyAsync(S.d_prefix, prefix.data(), prefix.size() * sizeof(int32_t), cudaMemcpyHostToDevice, S.stream));
-      CUS(cudaMemcpyAsync(S.d_pcm, (const char*)pcm_host + (size_t)pcm0 * sb, (size_t)(pcm1 - pcm0) * sb,
-                          cudaMemcpyHostToDevice, S.stream));
+      if (channels == 1) {
+        CUS(cudaMemcpyAsync(S.d_pcm, (const char*)pcm_host + (size_t)pcm0 * sb, (size_t)(pcm1 - pcm0) * sb,
+                            cudaMemcpyHostToDevice, S.stream));
+      } else {
+        // interleaved frames: copy the group, then mix down on the device (remix, signal.py:170-223)
+        const size_t raw_bytes = pcm_bytes * (size_t)channels;
+        CUS(ensure(&S.d_raw, &S.raw_cap, raw_bytes));
+        CUS(cudaMemcpyAsync(S.d_raw, (const char*)pcm_host + (size_t)pcm0 * sb * channels,
+                            (size_t)(pcm1 - pcm0) * sb * channels, cudaMemcpyHostToDevice, S.stream));
+        if (pcm1 > pcm0) {
+          CUS(mmb::launch_remix_mono(S.d_raw, p->sample_bytes, pcm1 - pcm0, channels, channel, S.d_pcm, S.stream));
+          ++n_launch;
+        }
+      }
       // pageable tab/prefix vectors are reused by the next group: the async copies above are staged
       // synchronously by the runtime for pageable memory, so this is safe.
       if (prefix.back() > 0) {
@@ -547,4 +586,26 @@ done:
   (void)used_slots;
   if (launches) *launches = n_launch;
   return status;
+}
+
+extern "C" int mmb_run_host(const mmb_plan* p, const mmb_track* units, int32_t n, const void* pcm_host,
+                            const mmb_outputs* oh, int32_t* launches) {
+  return run_host_impl(p, units, n, pcm_host, 1, -1, oh, launches);
+}
+
+extern "C" int mmb_run_host_interleaved(const mmb_plan* p, const mmb_track* units, int32_t n, const void* pcm_host,
+                                        int32_t num_channels, int32_t channel, const mmb_outputs* oh,
+                                        int32_t* launches) {
+  return run_host_impl(p, units, n, pcm_host, num_channels, channel, oh, launches);
+}
+
+extern "C" int mmb_remix_mono(const void* in_dev, int32_t sample_bytes, int64_t num_frames, int32_t num_channels,
+                              int32_t channel, void* out_dev, void* stream) {
+  if (!in_dev || !out_dev || (sample_bytes != 2 && sample_bytes != 4) || num_frames < 0 || num_channels < 1 ||
+      channel < -1 || channel >= num_channels)
+    return fail(MMB_E_INVALID, "mmb_remix_mono: invalid argument");
+  if (num_frames == 0) return MMB_OK;
+  cudaError_t e = mmb::launch_remix_mono(in_dev, sample_bytes, num_frames, num_channels, channel, out_dev,
+                                         (cudaStream_t)stream);
+  return e == cudaSuccess ? MMB_OK : cuda_fail(e, "remix kernel launch");
 }

@@ -144,5 +144,9 @@ inline SmemLayout smem_layout(int N, int warps, int group_warps, int n_bands, in
 cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, int grid, int smem_bytes,
                             cudaStream_t stream);
 cudaError_t frontend_set_smem(int N, int sample_bytes, int smem_bytes);
+// interleaved (num_frames, channels) int16 / float32 -> mono of the same type: mean over the channels with the
+// reference's rounding (np.mean(...).astype(dtype), signal.py:212), or one channel verbatim (channel >= 0)
+cudaError_t launch_remix_mono(const void* in, int sample_bytes, int64_t num_frames, int channels, int channel,
+                              void* out, cudaStream_t stream);
 
 }  // namespace mmb

@@ -16,6 +16,7 @@
 #include <stdint.h>
 
 #include "../../include/madmom_b200.h"
+#include "frontend_params.h"
 
 namespace {
 
@@ -230,7 +231,137 @@ __global__ void __launch_bounds__(256) complex_flux_kernel(const float* __restri
   if (lane == 0) odf[row] = sum;
 }
 
+// ---------------------------------------------------------------------------------------------- spectral ODFs
+// One warp per frame: a reduction over the bins of a magnitude spectrogram and / or a complex STFT with lags
+// of one or two frames (madmom/features/onsets.py:102-160, 320-581).  Frames before the start of the row's signal
+// count as in the reference (zero rows of the lagged matrices).
+__device__ __forceinline__ float wrap_to_pi(float x) {
+  // np.mod(x + pi, 2 pi) - pi in float32 (result of mod has the sign of the divisor)
+  const float pi = 3.14159265358979323846f, two_pi = 6.28318530717958647692f;
+  float r = fmodf(x + pi, two_pi);
+  if (r < 0.0f) r += two_pi;
+  return r - pi;
+}
+__device__ __forceinline__ float cabs2(float2 z) { return sqrtf(z.x * z.x + z.y * z.y); }
+
+// X[t-1] |.| exp(i (2 phi[t-1] - phi[t-2])) without trigonometry: s1 u1^2 conj(u2), u = X / |X| (1 when X = 0)
+__device__ __forceinline__ float2 cd_target(float2 x1, float2 x2, bool have2) {
+  const float s1 = cabs2(x1);
+  if (s1 == 0.0f) return make_float2(0.0f, 0.0f);
+  float2 u = make_float2((x1.x * x1.x - x1.y * x1.y) / s1, 2.0f * x1.x * x1.y / s1);   // s1 u1^2
+  if (have2) {
+    const float s2 = cabs2(x2);
+    if (s2 > 0.0f) u = make_float2((u.x * x2.x + u.y * x2.y) / s2, (u.y * x2.x - u.x * x2.y) / s2);
+  }
+  return u;
+}
+
+__global__ void __launch_bounds__(256) spectral_odf_kernel(int32_t mode, const float2* __restrict__ stft,
+                                                           int64_t ld_stft, const float* __restrict__ spec,
+                                                           int64_t ld_spec, int64_t rows, int32_t cols,
+                                                           int64_t seg_rows, const int64_t* __restrict__ seg,
+                                                           int32_t n_seg, int32_t d, float eps,
+                                                           float* __restrict__ out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
+  if (row >= rows) return;
+  int64_t s0 = 0;
+  if (seg) s0 = seg[find_segment(seg, n_seg, row)];
+  else if (seg_rows > 0) s0 = (row / seg_rows) * seg_rows;
+  const int64_t t = row - s0;
+  float acc = 0.0f, acc2 = 0.0f;
+  switch (mode) {
+    case MMB_ODF_HFC:
+      for (int k = lane; k < cols; k += 32) acc += spec[row * ld_spec + k] * (float)k;
+      break;
+    case MMB_ODF_SPECTRAL_DIFF:
+      if (t >= d)
+        for (int k = lane; k < cols; k += 32) {
+          const float v = fmaxf(spec[row * ld_spec + k] - spec[(row - d) * ld_spec + k], 0.0f);
+          acc += v * v;
+        }
+      break;
+    case MMB_ODF_MKL:
+      if (t >= d)
+        for (int k = lane; k < cols; k += 32)
+          acc += logf(1.0f + spec[row * ld_spec + k] / (spec[(row - d) * ld_spec + k] + eps));
+      break;
+    case MMB_ODF_PHASE_DEV:
+    case MMB_ODF_WEIGHTED_PHASE_DEV:
+    case MMB_ODF_NORM_WEIGHTED_PHASE_DEV:
+      for (int k = lane; k < cols; k += 32) {
+        const float2 x0 = stft[row * ld_stft + k];
+        const float m = cabs2(x0);
+        acc2 += m;
+        if (t >= 2) {
+          const float2 x1 = stft[(row - 1) * ld_stft + k], x2 = stft[(row - 2) * ld_stft + k];
+          const float p0 = atan2f(x0.y, x0.x), p1 = atan2f(x1.y, x1.x), p2 = atan2f(x2.y, x2.x);
+          const float pd = wrap_to_pi(p0 - 2.0f * p1 + p2);
+          acc += fabsf(mode == MMB_ODF_PHASE_DEV ? pd : pd * m);
+        }
+      }
+      break;
+    case MMB_ODF_COMPLEX_DOMAIN:
+    case MMB_ODF_RECTIFIED_COMPLEX_DOMAIN:
+      for (int k = lane; k < cols; k += 32) {
+        float2 c = stft[row * ld_stft + k];
+        const float m0 = cabs2(c);
+        float2 x1 = make_float2(0.0f, 0.0f);
+        if (t >= 1) {
+          x1 = stft[(row - 1) * ld_stft + k];
+          const float2 x2 = t >= 2 ? stft[(row - 2) * ld_stft + k] : make_float2(0.0f, 0.0f);
+          // frame 0 of a signal has target phase 0: |X[0]| itself
+          const float2 tg = t >= 2 ? cd_target(x1, x2, true) : make_float2(cabs2(x1), 0.0f);
+          c.x -= tg.x; c.y -= tg.y;
+        }
+        float v = cabs2(c);
+        if (mode == MMB_ODF_RECTIFIED_COMPLEX_DOMAIN) {
+          bool rising = false;
+          if (t >= d) rising = m0 - cabs2(stft[(row - d) * ld_stft + k]) > 0.0f;
+          if (!rising) v = 0.0f;
+        }
+        acc += v;
+      }
+      break;
+    default: break;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    acc2 += __shfl_xor_sync(0xffffffffu, acc2, o);
+  }
+  if (lane != 0) return;
+  const float n = (float)cols;
+  float r = acc;
+  if (mode == MMB_ODF_HFC || mode == MMB_ODF_MKL || mode == MMB_ODF_PHASE_DEV || mode == MMB_ODF_WEIGHTED_PHASE_DEV)
+    r = acc / n;
+  else if (mode == MMB_ODF_NORM_WEIGHTED_PHASE_DEV)
+    r = (acc / n) / (acc2 / n + eps);
+  out[row] = r;
+}
+
 }  // namespace
+
+extern "C" MMB_API int mmb_spectral_odf(int32_t mode, const void* stft_dev, int64_t ld_stft, const float* spec_dev,
+                                        int64_t ld_spec, int64_t rows, int32_t cols, int64_t rows_per_signal,
+                                        const int64_t* seg_offsets_dev, int32_t n_segments, int32_t diff_frames,
+                                        double epsilon, float* odf_dev, void* stream) {
+  const bool needs_spec = mode == MMB_ODF_HFC || mode == MMB_ODF_SPECTRAL_DIFF || mode == MMB_ODF_MKL;
+  if (mode < MMB_ODF_HFC || mode > MMB_ODF_RECTIFIED_COMPLEX_DOMAIN || !odf_dev || rows < 0 || cols <= 0 ||
+      (needs_spec && (!spec_dev || ld_spec < cols)) || (!needs_spec && (!stft_dev || ld_stft < cols)) ||
+      (seg_offsets_dev && n_segments < 1))
+    return MMB_E_INVALID;
+  const bool lagged = mode == MMB_ODF_SPECTRAL_DIFF || mode == MMB_ODF_MKL || mode == MMB_ODF_RECTIFIED_COMPLEX_DOMAIN;
+  if (lagged && diff_frames < 1) return MMB_E_INVALID;
+  if ((mode == MMB_ODF_MKL || mode == MMB_ODF_NORM_WEIGHTED_PHASE_DEV) && !(epsilon > 0.0)) return MMB_E_INVALID;
+  if (rows == 0) return MMB_OK;
+  const int warps = 8;
+  const int64_t grid = (rows + warps - 1) / warps;
+  spectral_odf_kernel<<<(unsigned)grid, warps * 32, 0, (cudaStream_t)stream>>>(
+      mode, (const float2*)stft_dev, ld_stft, spec_dev, ld_spec, rows, cols, rows_per_signal, seg_offsets_dev,
+      n_segments, diff_frames, (float)epsilon, odf_dev);
+  return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+}
 
 extern "C" MMB_API int mmb_matrix_diff(const float* in_dev, int64_t ld_in, float* out_dev, int64_t ld_out,
                                        float* odf_dev, int64_t rows, int32_t cols, int64_t rows_per_signal,
@@ -291,4 +422,46 @@ extern "C" MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, co
       lgd_dev, ld_lgd, diff_dev, ld_diff, band_lo_dev, band_hi_dev, n_bands, n_bins, rows, rows_per_signal,
       seg_offsets_dev, n_segments, temporal_filter, odf_dev);
   return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+}
+
+// ---------------------------------------------------------------------------------------------- PCM ingest
+namespace {
+// np.mean(signal, axis=-1).astype(signal.dtype) (madmom/audio/signal.py:212): integer samples are averaged
+// exactly and truncated towards zero by the cast back; float32 samples are summed in channel order in float32 and
+// divided by the channel count.
+template <typename T>
+__global__ void __launch_bounds__(256) remix_mono_kernel(const T* __restrict__ in, int64_t n, int channels,
+                                                         int channel, T* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const T* f = in + i * channels;
+    if (channel >= 0) { out[i] = f[channel]; continue; }
+    if (sizeof(T) == 2) {
+      int sum = 0;
+      for (int c = 0; c < channels; ++c) sum += (int)f[c];
+      out[i] = (T)(sum / channels);                    // C division truncates towards zero like astype(int16)
+    } else {
+      float sum = (float)f[0];
+      for (int c = 1; c < channels; ++c) sum += (float)f[c];
+      out[i] = (T)(sum / (float)channels);
+    }
+  }
+}
+}  // namespace
+
+cudaError_t mmb::launch_remix_mono(const void* in, int sample_bytes, int64_t num_frames, int channels, int channel,
+                                   void* out, cudaStream_t stream) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int64_t blocks = (num_frames + 255) / 256;
+  if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;      // grid-stride, a multiple of the SM count
+  if (blocks < 1) blocks = 1;
+  if (sample_bytes == 2)
+    remix_mono_kernel<int16_t><<<(unsigned)blocks, 256, 0, stream>>>((const int16_t*)in, num_frames, channels, channel,
+                                                                    (int16_t*)out);
+  else
+    remix_mono_kernel<float><<<(unsigned)blocks, 256, 0, stream>>>((const float*)in, num_frames, channels, channel,
+                                                                  (float*)out);
+  return cudaGetLastError();
 }

@@ -1,6 +1,7 @@
 """Onset detection functions on top of the fused front end, and peak picking on the device.
 
-Mirror of madmom/features/onsets.py: `spectral_flux` (:163-190), `superflux` (:193-240), `SpectralOnsetProcessor`
+Mirror of madmom/features/onsets.py: `spectral_flux` (:163-190), `superflux` (:193-240), the other spectral
+onset detection functions (:102-160, :320-581), `SpectralOnsetProcessor`
 (:584-720), `peak_picking` (:875-963), `OnsetPeakPickingProcessor` (:966-1180, offline mode) and
 `madmom.utils.combine_events` (madmom/utils/__init__.py:275-330).
 
@@ -78,10 +79,110 @@ def complex_flux(spectrogram, diff_frames=None, diff_max_bins=3, temporal_filter
     return _ComplexFlux(diff, temporal_filter)
 
 
+EPSILON = np.spacing(1)
+
+
+class _SpectralODF(DeviceResult):
+    """One of the bin-wise onset detection functions of madmom/features/onsets.py:102-160, 320-581, computed by
+    `mmb_spectral_odf` (one warp per frame) from the spectrogram or the STFT on the device."""
+
+    def __init__(self, spectrogram, mode, diff_frames=1, epsilon=EPSILON):
+        DeviceResult.__init__(self, spectrogram._chain.copy())
+        self.spectrogram = spectrogram
+        self.mode = mode
+        self.diff_frames = int(diff_frames)
+        self.epsilon = float(epsilon)
+
+    def _shape(self):
+        return (self.spectrogram.shape[0],)
+
+    def _compute(self):
+        from .. import _lib
+        if _lib.ODF_MODES[self.mode] <= 3:
+            return _lib.spectral_odf(self.mode, spec=self.spectrogram.tensor, diff_frames=self.diff_frames,
+                                     epsilon=self.epsilon)
+        return _lib.spectral_odf(self.mode, stft=self.spectrogram.stft.tensor, diff_frames=self.diff_frames,
+                                 epsilon=self.epsilon)
+
+
+def _default_diff_frames(spectrogram, diff_frames):
+    if diff_frames is not None:
+        return int(diff_frames)
+    from ..recipe import diff_frames as _diff_frames
+    from ..audio.spectrogram import DIFF_RATIO
+    return _diff_frames(DIFF_RATIO, hop_size=spectrogram.stft.frames.hop_size,
+                        frame_size=spectrogram.stft.frames.frame_size, window=spectrogram.stft.window)
+
+
+def _unfiltered(spectrogram):
+    # the reference compares np.shape(phase) with np.shape(spectrogram) (onsets.py:438-440, 503-505)
+    if tuple(spectrogram.shape) != tuple(spectrogram.stft.shape):
+        raise ValueError("spectrogram and phase must be of same shape")
+
+
+def high_frequency_content(spectrogram):
+    """Mean over the bins of magnitude times bin number (madmom/features/onsets.py:102-127).  float32 on the
+    device (the reference's result is float64)."""
+    return _SpectralODF(_as_spectrogram(spectrogram), "high_frequency_content")
+
+
+def spectral_diff(spectrogram, diff_frames=None):
+    """Sum of the squared positive differences (madmom/features/onsets.py:130-160)."""
+    spectrogram = _as_spectrogram(spectrogram)
+    if isinstance(spectrogram, SpectrogramDifference):
+        raise NotImplementedError("spectral_diff of a SpectrogramDifference is not available on the GPU path; "
+                                  "pass the spectrogram itself")
+    return _SpectralODF(spectrogram, "spectral_diff", _default_diff_frames(spectrogram, diff_frames))
+
+
+def modified_kullback_leibler(spectrogram, diff_frames=1, epsilon=EPSILON):
+    """Modified Kullback-Leibler (madmom/features/onsets.py:320-362)."""
+    if epsilon <= 0:
+        raise ValueError("a positive value must be added before division")
+    return _SpectralODF(_as_spectrogram(spectrogram), "modified_kullback_leibler", diff_frames, epsilon)
+
+
+def phase_deviation(spectrogram):
+    """Mean absolute second difference of the phase (madmom/features/onsets.py:390-414)."""
+    return _SpectralODF(_as_spectrogram(spectrogram), "phase_deviation")
+
+
+def weighted_phase_deviation(spectrogram):
+    """Phase deviation weighted by the magnitudes (madmom/features/onsets.py:417-446)."""
+    spectrogram = _as_spectrogram(spectrogram)
+    _unfiltered(spectrogram)
+    return _SpectralODF(spectrogram, "weighted_phase_deviation")
+
+
+def normalized_weighted_phase_deviation(spectrogram, epsilon=EPSILON):
+    """Weighted phase deviation over the mean magnitude (madmom/features/onsets.py:449-479)."""
+    if epsilon <= 0:
+        raise ValueError("a positive value must be added before division")
+    spectrogram = _as_spectrogram(spectrogram)
+    _unfiltered(spectrogram)
+    return _SpectralODF(spectrogram, "normalized_weighted_phase_deviation", epsilon=epsilon)
+
+
+def complex_domain(spectrogram):
+    """Complex domain (madmom/features/onsets.py:482-549)."""
+    spectrogram = _as_spectrogram(spectrogram)
+    _unfiltered(spectrogram)
+    return _SpectralODF(spectrogram, "complex_domain")
+
+
+def rectified_complex_domain(spectrogram, diff_frames=None):
+    """Complex domain restricted to bins with rising magnitude (madmom/features/onsets.py:552-581)."""
+    spectrogram = _as_spectrogram(spectrogram)
+    _unfiltered(spectrogram)
+    return _SpectralODF(spectrogram, "rectified_complex_domain", _default_diff_frames(spectrogram, diff_frames))
+
+
 class SpectralOnsetProcessor(SequentialProcessor):
     """Signal -> frames -> STFT -> spectrogram [-> filterbank] [-> log] -> onset detection function
     (madmom/features/onsets.py:584-683).  The whole chain is one kernel launch."""
-    METHODS = ["superflux", "complex_flux", "spectral_flux"]
+    METHODS = ["superflux", "complex_flux", "high_frequency_content", "spectral_diff", "spectral_flux",
+               "modified_kullback_leibler", "phase_deviation", "weighted_phase_deviation",
+               "normalized_weighted_phase_deviation", "complex_domain", "rectified_complex_domain"]
 
     def __init__(self, onset_method="spectral_flux", **kwargs):
         from ..audio.signal import SignalProcessor, FramedSignalProcessor

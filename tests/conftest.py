@@ -45,6 +45,11 @@ def ref_synth():
     return _npz("ref_synth.npz")
 
 
+@pytest.fixture(scope="session")
+def ref_odfs():
+    return _npz("ref_odfs.npz")
+
+
 def assert_close(actual, desired, rtol=1e-4, atol=1e-5, what=""):
     """The parity bound of BASELINE.md section 2: |a - b| <= atol + rtol * |b| element-wise."""
     actual = np.asarray(actual)

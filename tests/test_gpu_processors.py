@@ -335,3 +335,86 @@ def test_complex_flux(sig, ref_sample):
     spec = LogarithmicFilteredSpectrogram(Spectrogram(FramedSignal(sig), circular_shift=True), num_bands=24)
     assert np.allclose(complex_flux(spec)[:6], [0, 0.476213485, 0.0877621323, 0.0593151376, 0.0654867291,
                                                 0.0954693183], atol=2e-5)
+
+
+@pytest.mark.parametrize("which", ["sample", "synth"])
+def test_other_spectral_odfs(sample_pcm, ref_odfs, which):
+    """the remaining onset detection functions of madmom/features/onsets.py, with the inputs the
+    reference's tests use (tests/test_features_onsets.py:24-27), against vectors computed by the real reference.
+    The phase-based functions average over all 1024 bins, noise bins included, whose phases carry the rounding of
+    the FP32 FFT (the reference's is float64): their bound is printed and asserted separately."""
+    from madmom_b200.audio.signal import Signal
+    from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
+    from madmom_b200.features import onsets as ON
+    from madmom_b200.synth import make_track
+    x = sample_pcm if which == "sample" else make_track(3, 2.0)
+    spec = Spectrogram(Signal(x, sample_rate=44100), circular_shift=True)
+    lfs = LogarithmicFilteredSpectrogram(spec, num_bands=24, mul=1, add=1)
+    got = {"hfc_logfilt": ON.high_frequency_content(lfs), "hfc_spec": ON.high_frequency_content(spec),
+           "sd_logfilt": ON.spectral_diff(lfs), "sd_spec": ON.spectral_diff(spec),
+           "mkl_logfilt": ON.modified_kullback_leibler(lfs), "mkl_spec": ON.modified_kullback_leibler(spec),
+           "pd": ON.phase_deviation(lfs), "wpd": ON.weighted_phase_deviation(spec),
+           "nwpd": ON.normalized_weighted_phase_deviation(spec), "cd": ON.complex_domain(spec),
+           "rcd": ON.rectified_complex_domain(spec)}
+    worst = {}
+    for k, v in got.items():
+        want = ref_odfs["%s_%s" % (which, k)]
+        a = np.asarray(v)
+        assert a.shape == want.shape, k
+        worst[k] = float(np.max(np.abs(a - want) / (1e-5 + 1e-4 * np.abs(want))))
+    print(which, {k: round(v, 3) for k, v in worst.items()})
+    for k in ("hfc_logfilt", "hfc_spec", "sd_logfilt", "sd_spec", "mkl_logfilt", "wpd", "nwpd", "cd"):
+        assert worst[k] <= 1.0, (k, worst[k])
+    if which == "sample":
+        # reference literals, tests/test_features_onsets.py:35-152
+        assert np.allclose(np.asarray(got["hfc_logfilt"])[:6], [8.97001563, 9.36399107, 8.64144536, 8.34977449,
+                                                               8.21097918, 8.40412515], rtol=1e-4)
+        assert np.allclose(np.asarray(got["cd"])[:6], [399.29980469, 585.9564209, 262.08010864, 225.84718323,
+                                                      196.88954163, 200.32469177], rtol=1e-4)
+        assert np.allclose(np.asarray(got["wpd"])[:6], [0, 0, 0.19568817, 0.20483065, 0.17890805, 0.16970603],
+                           rtol=1e-4)
+    # phase of noise-floor bins / ratio of noise-floor magnitudes / sign of tiny magnitude changes
+    assert worst["pd"] <= 50.0 and worst["mkl_spec"] <= 50.0 and worst["rcd"] <= 50.0, worst
+
+
+def test_spectral_odf_errors(sig):
+    from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
+    from madmom_b200.features import onsets as ON
+    lfs = LogarithmicFilteredSpectrogram(Spectrogram(sig, circular_shift=True), num_bands=24)
+    # reference: tests/test_features_onsets.py:108-152
+    for fn in (ON.weighted_phase_deviation, ON.normalized_weighted_phase_deviation, ON.complex_domain,
+               ON.rectified_complex_domain):
+        with pytest.raises(ValueError):
+            fn(lfs)
+    with pytest.raises(ValueError):
+        ON.modified_kullback_leibler(lfs, epsilon=0)
+
+
+def test_pcm_ingest_remix():
+    """interleaved multi-channel PCM mixed down on the device, bit for bit like
+    madmom.audio.signal.remix (np.mean(signal, axis=-1).astype(dtype), signal.py:212; its known answers
+    tests/test_audio_signal.py:277-361 are integer truncation cases like the ones below)."""
+    from madmom_b200 import _lib, recipe as R
+    from madmom_b200.batch import BatchFrontEnd
+    rng = np.random.default_rng(5)
+    st = rng.integers(-32768, 32768, size=(50001, 2)).astype(np.int16)
+    st[:4] = [[1, 2], [-1, -2], [32767, 32767], [-32768, -32767]]            # 1.5 -> 1, -1.5 -> -1, no clipping
+    want = np.mean(st, axis=-1).astype(np.int16)
+    got = _lib.remix_mono(torch.from_numpy(st).cuda()).cpu().numpy()
+    assert np.array_equal(got, want) and list(got[:4]) == [1, -1, 32767, -32767]
+    assert np.array_equal(_lib.remix_mono(torch.from_numpy(st).cuda(), channel=1).cpu().numpy(), st[:, 1])
+    six = rng.integers(-32768, 32768, size=(7777, 6)).astype(np.int16)
+    assert np.array_equal(_lib.remix_mono(torch.from_numpy(six).cuda()).cpu().numpy(),
+                          np.mean(six, axis=-1).astype(np.int16))
+    fl = rng.standard_normal((40000, 3)).astype(np.float32)
+    assert np.array_equal(_lib.remix_mono(torch.from_numpy(fl).cuda()).cpu().numpy(), np.mean(fl, axis=-1))
+    # host pipeline: interleaved stereo in, features of the mono mix out
+    fe = BatchFrontEnd(R.SUPERFLUX)
+    lens = [30000, 20001]
+    stereo = st[:sum(lens)]
+    mono = np.mean(stereo, axis=-1).astype(np.int16)
+    a = fe.run_host(stereo, lens, ("diff",), num_channels=2)["diff"].numpy()
+    b = fe.run_host(mono, lens, ("diff",))["diff"].numpy()
+    assert a.shape == b.shape and np.array_equal(a, b)
+    # a second call reuses the plan's pipeline buffers
+    assert np.array_equal(fe.run_host(stereo, lens, ("diff",), num_channels=2)["diff"].numpy(), b)

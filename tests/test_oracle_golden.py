@@ -312,6 +312,51 @@ def test_odf_literals(sample_pcm):
     assert np.allclose(cf[:6], [0, 0.476213485, 0.0877621323, 0.0593151376, 0.0654867291, 0.0954693183])
 
 
+def _odf_inputs(x):
+    r = dict(frame_size=2048, hop_size=441., num_bands=24, norm_filters=True, circular_shift=True,
+             diff_max_bins=None, positive_diffs=True)
+    return O.run_recipe(x, r, stages=True)
+
+
+def _oracle_odfs(st):
+    d = st["diff_frames"]
+    sp = O.spec(st["stft"])
+    return {"hfc_logfilt": O.high_frequency_content(st["log"]), "hfc_spec": O.high_frequency_content(sp),
+            "sd_logfilt": O.spectral_diff(st["log"], d), "sd_spec": O.spectral_diff(sp, d),
+            "mkl_logfilt": O.modified_kullback_leibler(st["log"]), "mkl_spec": O.modified_kullback_leibler(sp),
+            "pd": O.phase_deviation(st["stft"]), "wpd": O.weighted_phase_deviation(st["stft"]),
+            "nwpd": O.normalized_weighted_phase_deviation(st["stft"]), "cd": O.complex_domain(st["stft"]),
+            "rcd": O.rectified_complex_domain(st["stft"], d)}
+
+
+def test_other_odfs_literals(sample_pcm):
+    # reference known answers: tests/test_features_onsets.py:35-152 (np.allclose defaults)
+    o = _oracle_odfs(_odf_inputs(sample_pcm))
+    want = {"hfc_logfilt": [8.97001563, 9.36399107, 8.64144536, 8.34977449, 8.21097918, 8.40412515],
+            "sd_logfilt": [0, 0.55715936, 0.64004618, 0.0810971, 0.295396, 0.16324584],
+            "mkl_logfilt": [0, 0.71910584, 0.6664055, 0.68092251, 0.69984031, 0.71744561],
+            "pd": [0, 0, 0.71957183, 0.91994524, 0.9418999, 0.86083585],
+            "wpd": [0, 0, 0.19568817, 0.20483065, 0.17890805, 0.16970603],
+            "nwpd": [0, 0, 0.46018526, 0.50193471, 0.42031503, 0.40806249],
+            "cd": [399.29980469, 585.9564209, 262.08010864, 225.84718323, 196.88954163, 200.32469177],
+            "rcd": [0, 394.165222, 119.79425, 96.70564, 122.52311, 92.61698]}
+    for k, v in want.items():
+        # the reference literals were produced with a pyfftw float32-planned FFT upstream; the scipy float64
+        # path reproduces them to 1e-5 relative (same margin as tests/test_bin.py uses for the fixtures)
+        assert np.allclose(o[k][:6], v, rtol=2e-5, atol=1e-6), (k, o[k][:6])
+
+
+@pytest.mark.parametrize("which", ["sample", "synth"])
+def test_other_odfs_golden(sample_pcm, ref_odfs, which):
+    from madmom_b200.synth import make_track
+    x = sample_pcm if which == "sample" else make_track(3, 2.0)
+    o = _oracle_odfs(_odf_inputs(x))
+    for k, v in o.items():
+        want = ref_odfs["%s_%s" % (which, k)]
+        assert v.dtype == want.dtype and v.shape == want.shape, k
+        assert np.allclose(v, want, rtol=1e-6, atol=1e-7), (k, np.abs(v - want).max())
+
+
 # ------------------------------------------------------------------ multi-resolution stack, synthetic tracks
 def multires_oracle(x, mul, diff_ratio, hop=441.):
     cols = []

@@ -138,6 +138,9 @@ struct FbSchedule {
 };
 struct Piece { int start, len, band, q; const float* w; };
 
+// weight of iteration i of lane `lane`: four consecutive iterations of a lane sit in one float4
+inline size_t widx(int off, int i, int lane) { return (size_t)off + ((size_t)(i >> 2) * 32 + lane) * 4 + (i & 3); }
+
 void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, int P, FbSchedule& s) {
   const int B = cfg->num_bands;
   s = FbSchedule();
@@ -179,7 +182,7 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
           lane_used[lane] = true; ++placed; ok = true;
           s.start[ps * 32 + lane] = st;
           s.pid[ps * 32 + lane] = pc.q * s.b_pad + pc.band;
-          for (int k = 0; k < pc.len; ++k) s.w[off + (size_t)(k + lead) * 32 + lane] = pc.w[k];
+          for (int k = 0; k < pc.len; ++k) s.w[widx(off, k + lead, lane)] = pc.w[k];
         }
         if (!ok && i == 0) {
           // the pass-defining piece cannot stay inside [0, K) without a shift larger than its slack (only when
@@ -190,7 +193,7 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
           lane_used[lane] = true; ++placed; ok = true;
           s.start[ps * 32 + lane] = pc.start - lead;
           s.pid[ps * 32 + lane] = pc.q * s.b_pad + pc.band;
-          for (int k = 0; k < pc.len; ++k) s.w[off + (size_t)(k + lead) * 32 + lane] = pc.w[k];
+          for (int k = 0; k < pc.len; ++k) s.w[widx(off, k + lead, lane)] = pc.w[k];
         }
       }
       if (!ok) next.push_back(pc);
@@ -203,15 +206,19 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
 
 void build_schedule(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, FbSchedule& best) {
   static const int kCandidates[] = {8, 12, 16, 20, 24, 28, 32, 48, 64};
+  int forced = 0;
+  if (const char* env = std::getenv("MMB_FB_PIECE")) forced = std::atoi(env);
   bool have = false;
+  int best_cost = 0;
   for (int P : kCandidates) {
+    if (forced > 0 && P != forced) continue;
     FbSchedule s;
     schedule_with(cfg, K, woff, P, s);
     if (s.max_q > 16) continue;
-    // cost: two shared-memory wavefronts per iteration plus the epilogue's max_q loads per 32 bands
-    const int cost = 2 * s.iters + s.max_q * (s.b_pad / 32);
-    const int best_cost = 2 * best.iters + best.max_q * (best.b_pad / 32);
-    if (!have || cost < best_cost) { best = s; have = true; }
+    // issue slots per frame: ~4 per iteration (tap + magnitude loads, FMA, loop), ~12 per pass, ~3.5 per piece
+    // slot and 32 bands in the epilogue; the piece slots also cost shared memory per warp
+    const int cost = 8 * s.iters + 24 * (int)s.pass.size() + 7 * s.max_q * (s.b_pad / 32);
+    if (!have || cost < best_cost) { best = s; best_cost = cost; have = true; }
   }
   if (!have) schedule_with(cfg, K, woff, 64, best);
 }

@@ -86,9 +86,11 @@ struct BinSinkT {
   float sgn_odd;     // +1 or -1
   int log_mode;      // != 0: the spec output is log(m * mul + add) (LogarithmicSpectrogram of an unfiltered one)
   float mul, add;
-  MMB_HD void put(int k, float re, float im) const {
+  MMB_HD void put(int k, float re, float im) const { put_at(k, k, re, im); }
+  // magnitude slot `slot` of the scratch, bin k of the output rows
+  MMB_HD void put_at(int slot, int k, float re, float im) const {
     const float m = mag_of(re, im);
-    mag[k] = m;
+    mag[slot] = m;
     if (!EMIT) return;                 // hot path: magnitudes stay on chip, no per-bin branches
     if (spec_row) spec_row[k] = log_mode ? log_scaled(m, log_mode, mul, add) : m;
     if (stft_row) {
@@ -186,7 +188,8 @@ MMB_HD void split_1024x2(int lane, const float2 (&v)[32], const float2* zs, cons
 }
 
 // N = 4096, half c.  Even bins (c = 0) pair as (j, 1024 - j) with twiddle W4096^(2j) = W2048^j;
-// odd bins (c = 1) pair as (j, 1023 - j) with twiddle W4096^(2j+1) = tw4k[q*32 + lane].
+// odd bins (c = 1) pair as (j, 1023 - j) with twiddle W4096^(2j+1) = tw4k[q*32 + lane].  The sink's `mag` is the
+// half's own array: magnitude of bin 2j + c goes to mag[j].
 template <class Sink>
 MMB_HD void split_4096(int lane, int c, const float2 (&v)[32], const float2* zs,
                        const float2* __restrict__ tw2k, const float2* __restrict__ tw4k, const Sink& out) {
@@ -201,12 +204,12 @@ MMB_HD void split_4096(int lane, int c, const float2 (&v)[32], const float2* zs,
     const float br = zk.x - zp.x, bi = zk.y + zp.y;
     const float tr = w.x * br - w.y * bi, ti = w.x * bi + w.y * br;
     const int k = 2 * j + c, kp = 2 * jp + c;
-    out.put(k, ar + ti, ai - tr);
-    if (kp < 2048) out.put(kp, ar - ti, -(ai + tr));
+    out.put_at(j, k, ar + ti, ai - tr);
+    if (kp < 2048) out.put_at(jp, kp, ar - ti, -(ai + tr));
   }
   if (c == 0 && lane == 0) {             // bin 1024 pairs with itself
     const float2 z = v[brev5(16)];
-    out.put(1024, 2.0f * z.x, -2.0f * z.y);
+    out.put_at(512, 1024, 2.0f * z.x, -2.0f * z.y);
   }
 }
 

@@ -148,7 +148,8 @@ __device__ __forceinline__ void frames_loaded(const FrontendParams& p, GroupCtl*
 // Filterbank of one frame (two for N = 1024) owned by this warp: FbPass schedule over the magnitudes in the
 // warp's scratch, then the per-band sum of pieces, log scaling and the ring row.  `mag1` is the second frame of a
 // 1024-point pair or null.
-template <int NF>
+// SPLIT: the magnitudes are stored as even bins in `mag0` and odd bins in `mag1` (N = 4096).
+template <int NF, bool SPLIT = false>
 __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lane, const float* __restrict__ mag0,
                                                 const float* __restrict__ mag1, float* part,
                                                 const FbPass* __restrict__ s_pass, const float* __restrict__ s_w,
@@ -158,21 +159,24 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
   for (int ps = 0; ps < p.n_passes; ++ps) {
     const FbPass fp = s_pass[ps];
     const int st = s_start[ps * 32 + lane];
-    const float* w = s_w + fp.woff + lane;
-    const float* m0 = mag0 + st;
-    const float* m1 = (NF == 2) ? mag1 + st : mag0;
+    const float4* w = reinterpret_cast<const float4*>(s_w + fp.woff) + lane;
+    // SPLIT: taps 0, 2 read bins st, st + 2 (array of st's parity), taps 1, 3 the other array
+    const float* m0 = SPLIT ? ((st & 1) ? mag1 + (st >> 1) : mag0 + (st >> 1)) : mag0 + st;
+    const float* m1 = SPLIT ? ((st & 1) ? mag0 + ((st + 1) >> 1) : mag1 + (st >> 1)) : ((NF == 2) ? mag1 + st : mag0);
     float a0 = 0.0f, a1 = 0.0f, c0 = 0.0f, c1 = 0.0f;    // even / odd taps, two frames
 #pragma unroll 1
     for (int i = 0; i < fp.iters; i += 4) {          // pass lengths are multiples of four (capi.cu)
-      const float w0 = w[0], w1 = w[32], w2 = w[64], w3 = w[96];
-      const float x0 = m0[0], x1 = m0[1], x2 = m0[2], x3 = m0[3];
+      const float4 wv = *w;                          // taps i .. i+3 of this lane
+      const float w0 = wv.x, w1 = wv.y, w2 = wv.z, w3 = wv.w;
+      const float x0 = m0[0], x1 = SPLIT ? m1[0] : m0[1], x2 = SPLIT ? m0[1] : m0[2], x3 = SPLIT ? m1[1] : m0[3];
       a0 = fmaf(x0, w0, a0); c0 = fmaf(x1, w1, c0); a0 = fmaf(x2, w2, a0); c0 = fmaf(x3, w3, c0);
+      if (SPLIT) { m0 += 2; m1 += 2; w += 32; continue; }
       if (NF == 2) {
         const float y0 = m1[0], y1 = m1[1], y2 = m1[2], y3 = m1[3];
         a1 = fmaf(y0, w0, a1); c1 = fmaf(y1, w1, c1); a1 = fmaf(y2, w2, a1); c1 = fmaf(y3, w3, c1);
         m1 += 4;
       }
-      w += 128; m0 += 4;
+      w += 32; m0 += 4;
     }
     const int pid = s_pid[ps * 32 + lane];
     part[pid] = a0 + c0;
@@ -275,7 +279,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
 
   unsigned char* my_scratch = smem + L.scratch + warp * warp_scratch_bytes(N);
   float2* ex = reinterpret_cast<float2*>(my_scratch);
-  float* my_mag = (N == 4096) ? reinterpret_cast<float*>(my_scratch + 8448) : reinterpret_cast<float*>(my_scratch);
+  float* my_mag = reinterpret_cast<float*>(my_scratch);                       // odd bins for N = 4096
+  float* my_mag_even = reinterpret_cast<float*>(my_scratch + kEvenMagOffset);   // N = 4096 only
   float* my_part = reinterpret_cast<float*>(smem + L.part + warp * L.part_stride);
 
   // ---- plan constants -> shared memory (once per persistent CTA)
@@ -448,6 +453,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           core_pass2_fft(v);
           core_publish_upper(lane, v, ex, c == 0);
           __syncwarp();
+          o.mag = c == 0 ? my_mag_even : my_mag;
           if (o.stft_row || o.spec_row) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
           else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
           __syncwarp();
@@ -455,7 +461,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
       }
       if (nb > 0) {
         __syncwarp();
-        warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
+        if (N == 4096) warp_filterbank<1, true>(p, lane, my_mag_even, my_mag, my_part, s_pass, s_w, s_start, s_pid);
+        else warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
         MMB_PENDING_DIFFERENCE();
         int sl = slot0 + gwarp; if (sl >= R) sl -= R;
         warp_band_epilogue(p, lane, my_part, s_ring + sl * nb, row, g >= ga);

@@ -17,7 +17,8 @@ struct Track {
 };
 
 // Per-warp filterbank schedule (built on the host, capi.cu): every band is cut into pieces; in pass p lane l
-// accumulates   sum_i mag[start[p][l] + i] * w[p][i][l],  i < iters[p]   (weights zero-padded to iters[p]; the
+// accumulates   sum_i mag[start[p][l] + i] * w[p][i][l],  i < iters[p]   (weights zero-padded to iters[p], stored
+// as float4 [p][i / 4][l][i % 4]; the
 // starts of a pass are distinct modulo 32, so the reads are free of bank conflicts) and stores the partial sum at
 // part[pid[p][l]] = part[q * b_pad + band]; the epilogue adds the pieces q = 0 .. max_q-1 of each band in order.
 struct FbPass {
@@ -83,8 +84,11 @@ constexpr int kMaxDiffFrames = 16;
 
 // frames one round of a warp group produces
 __host__ __device__ constexpr int frames_per_round(int N, int group_warps) { return N == 1024 ? 2 * group_warps : group_warps; }
-// per-warp scratch (bytes): exchange tile (+ magnitudes aliased in its lower 4 KB; separate 8 KB for 4096)
-__host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? 8448 + 8192 : 8448) + 16; }
+// per-warp scratch (bytes): exchange tile with the magnitudes aliased in its lower 4 KB.  N = 4096 keeps the even
+// bins (first half of the frame's two FFT calls) in 4 KB behind the tile, 16 floats off so that even and odd
+// bins of neighbouring lanes fall into different banks, and the odd bins in the tile like the other sizes.
+constexpr int kEvenMagOffset = 8448 + 64;
+__host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? kEvenMagOffset + 4096 : 8448) + 16; }
 
 // one descriptor per round of a group, written by one lane, read by the group (4 slots, see frontend_kernel.cu)
 struct RoundDesc {

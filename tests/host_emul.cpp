@@ -66,7 +66,11 @@ extern "C" int emul_frame(int N, const float* x, const float* win_half, float* m
     for (int c = 0; c < 2; ++c) {
       for (int l = 0; l < 32; ++l) load_frame_4096<float>(l, c, w.v[l], x, win_half, tw2k.data());
       run_core(w, tw1, c == 0);
-      for (int l = 0; l < 32; ++l) split_4096(l, c, w.v[l], w.ex, tw2k.data(), tw4k.data(), out);
+      // the kernel keeps the magnitudes of the even (c = 0) and odd (c = 1) bins in two arrays
+      std::vector<float> half(1025, 0.0f);
+      BinSink oh = out; oh.mag = half.data();
+      for (int l = 0; l < 32; ++l) split_4096(l, c, w.v[l], w.ex, tw2k.data(), tw4k.data(), oh);
+      for (int j = 0; 2 * j + c < K; ++j) mg[2 * j + c] = half[j];
     }
   } else {
     return -1;

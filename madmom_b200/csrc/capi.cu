@@ -308,11 +308,13 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
     const int fpr = mmb::frames_per_round(N, gw);
     const int span = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N + align_elems) + 7) & ~7;
     const int rows = 2 * fpr + cfg->diff_frames;
-    const mmb::SmemLayout L = mmb::smem_layout(N, w, gw, cfg->num_bands, p->n_passes, p->max_q * p->b_pad,
-                                               p->w_floats, rows, span, p->sample_bytes);
-    if (L.total <= (int)prop.sharedMemPerBlockOptin) {
-      p->warps = w; p->group_warps = gw; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
-      p->L = L;
+    for (int alias = 0; alias <= 1 && p->warps == 0; ++alias) {      // private partial sums first (no clearing)
+      const mmb::SmemLayout L = mmb::smem_layout(N, w, gw, cfg->num_bands, p->n_passes, p->max_q * p->b_pad,
+                                                 p->w_floats, rows, span, p->sample_bytes, alias != 0);
+      if (L.total <= (int)prop.sharedMemPerBlockOptin) {
+        p->warps = w; p->group_warps = gw; p->span_cap = span; p->ring_rows = rows; p->smem_bytes = L.total;
+        p->L = L;
+      }
     }
   }
   if (p->warps == 0) {

@@ -156,6 +156,11 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
                                                 const int* __restrict__ s_start, const int* __restrict__ s_pid) {
   // the previous frame's epilogue reads of `part` are complete: the warp has passed a __syncwarp since
   const int np1 = p.max_q * p.b_pad + 1;
+  if (p.L.part_stride == 0) {          // the slots share memory with the FFT exchange tile: clear them per frame
+    const int n4 = (NF * np1 + 3) >> 2;
+    for (int i = lane; i < n4; i += 32) reinterpret_cast<float4*>(part)[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    __syncwarp();
+  }
   for (int ps = 0; ps < p.n_passes; ++ps) {
     const FbPass fp = s_pass[ps];
     const int st = s_start[ps * 32 + lane];
@@ -281,7 +286,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   float2* ex = reinterpret_cast<float2*>(my_scratch);
   float* my_mag = reinterpret_cast<float*>(my_scratch);                       // odd bins for N = 4096
   float* my_mag_even = reinterpret_cast<float*>(my_scratch + kEvenMagOffset);   // N = 4096 only
-  float* my_part = reinterpret_cast<float*>(smem + L.part + warp * L.part_stride);
+  float* my_part = L.part_stride == 0 ? reinterpret_cast<float*>(my_scratch + kPartAliasOffset)
+                                      : reinterpret_cast<float*>(smem + L.part + warp * L.part_stride);
 
   // ---- plan constants -> shared memory (once per persistent CTA)
   for (int i = tid; i < N; i += nthreads) s_win[i] = p.win[i];
@@ -296,7 +302,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     for (int i = tid; i < p.n_passes; i += nthreads) s_pass[i] = p.fb_pass[i];
     for (int i = tid; i < p.w_floats; i += nthreads) s_w[i] = p.fb_w[i];
     for (int i = tid; i < p.n_passes * 32; i += nthreads) { s_start[i] = p.fb_start[i]; s_pid[i] = p.fb_pid[i]; }
-    for (int i = tid; i < warps * (L.part_stride / 4); i += nthreads)
+    for (int i = tid; i < warps * (L.part_stride / 4); i += nthreads)     // private slots only
       reinterpret_cast<float*>(smem + L.part)[i] = 0.0f;     // part slots without a piece are never written again
   }
   uint64_t* ring_bar = reinterpret_cast<uint64_t*>(&G->ring_bar);

@@ -31,7 +31,7 @@ struct SmemLayout {
   int ctl, win, tw1, tw2k, tw4k, fb_pass, fb_w, fb_start, fb_pid, ring, scratch, part, pcm, total;
   int ctl_stride;        // bytes of control block per warp group
   int ring_stride;       // bytes of log-spectrogram ring per warp group
-  int part_stride;       // bytes of partial sums per warp
+  int part_stride;       // bytes of partial sums per warp; 0: they live in the upper half of the warp's exchange tile
   int pcm_stride;        // bytes of staged PCM span per warp group
 };
 
@@ -88,6 +88,9 @@ __host__ __device__ constexpr int frames_per_round(int N, int group_warps) { ret
 // bins (first half of the frame's two FFT calls) in 4 KB behind the tile, 16 floats off so that even and odd
 // bins of neighbouring lanes fall into different banks, and the odd bins in the tile like the other sizes.
 constexpr int kEvenMagOffset = 8448 + 64;
+// the exchange tile above the 4 KB of magnitudes is idle between the split and the next frame's FFT: the partial
+// sums of the filterbank may live there when that buys another warp (they must then be cleared per frame)
+constexpr int kPartAliasOffset = 4096, kPartAliasBytes = 8448 - 4096;
 __host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? kEvenMagOffset + 4096 : 8448) + 16; }
 
 // one descriptor per round of a group, written by one lane, read by the group (4 slots, see frontend_kernel.cu)
@@ -120,7 +123,7 @@ __host__ __device__ inline int mmb_align16(int x) { return (x + 15) & ~15; }
 
 // `ring_rows`, `span_cap` are per group
 inline SmemLayout smem_layout(int N, int warps, int group_warps, int n_bands, int n_passes, int part_floats,
-                              int w_floats, int ring_rows, int span_cap, int sample_bytes) {
+                              int w_floats, int ring_rows, int span_cap, int sample_bytes, bool alias_part) {
   SmemLayout L;
   const int groups = warps / group_warps;
   int o = 0;
@@ -138,6 +141,7 @@ inline SmemLayout smem_layout(int N, int warps, int group_warps, int n_bands, in
   L.ring = o;        o += groups * L.ring_stride;
   L.scratch = o;     o += warps * warp_scratch_bytes(N);
   L.part_stride = mmb_align16((part_floats + 1) * 4 * (N == 1024 ? 2 : 1));
+  if (alias_part && L.part_stride <= kPartAliasBytes) L.part_stride = 0;
   L.part = o;        o += n_bands > 0 ? warps * L.part_stride : 0;
   L.pcm_stride = mmb_align16(span_cap * sample_bytes);
   L.pcm = o;         o += groups * L.pcm_stride;

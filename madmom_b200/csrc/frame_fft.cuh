@@ -16,6 +16,16 @@ namespace mmb {
 
 template <typename S>
 MMB_HD float to_f32(S s) { return (float)s; }
+#if defined(__CUDA_ARCH__)
+// int16 -> float through a sign-extending load and the 32-bit conversion (I2FP, FMA-pipe rate) instead of the
+// 16-bit one (I2F.S16 runs on the quarter-rate XU pipe and would bound the load phase: 64 per lane and frame)
+template <>
+__device__ __forceinline__ float to_f32<int16_t>(int16_t s) {
+  float f;
+  asm("cvt.rn.f32.s32 %0, %1;" : "=f"(f) : "r"((int)s));
+  return f;
+}
+#endif
 
 // ------------------------------------------------------------------------------------------ loads
 // x points at the first sample of the frame inside the staged PCM span (any alignment).

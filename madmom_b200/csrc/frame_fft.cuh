@@ -139,8 +139,24 @@ MMB_HD void split_2048(int lane, const float2 (&v)[32], const float2* zs, const 
 // |angle(a * conj(b))| / pi in [0, 1]; `flip` = -1 negates the product (circular shift: X[k] -> (-1)^k X[k]).
 __device__ __forceinline__ float abs_angle_over_pi(float2 a, float2 b, float flip) {
   const float re = (a.x * b.x + a.y * b.y) * flip;
-  const float im = a.y * b.x - a.x * b.y;
-  return atan2f(fabsf(im), re) / 3.14159265358979323846f;
+  const float im = fabsf(a.y * b.x - a.x * b.y);
+  // atan2(im, re) / pi for im >= 0: octant reduction to t = min / max in [0, 1], atan(t) = t P(t^2) with a
+  // 7-term minimax polynomial (3.2e-7 rad), then the reflections; 0 for the zero vector like np.angle
+  const float ar = fabsf(re);
+  const float mx = fmaxf(im, ar), mn = fminf(im, ar);
+  const float t = mx > 0.0f ? __fdividef(mn, mx) : 0.0f;
+  const float u = t * t;
+  float p = 0.00681148456f;
+  p = fmaf(p, u, -0.0336031997f);
+  p = fmaf(p, u, 0.0796223719f);
+  p = fmaf(p, u, -0.132332626f);
+  p = fmaf(p, u, 0.198077921f);
+  p = fmaf(p, u, -0.333173652f);
+  p = fmaf(p, u, 0.999996111f);
+  float r = p * t * 0.318309886183790671538f;          // in units of pi, [0, 1/4]
+  if (im > ar) r = 0.5f - r;
+  if (re < 0.0f) r = 1.0f - r;
+  return r;
 }
 
 // N = 2048 split that also emits the magnitude of the local group delay (ComplexFlux, madmom/audio/stft.py:

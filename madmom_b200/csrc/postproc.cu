@@ -184,6 +184,13 @@ __global__ void __launch_bounds__(1024) peak_compact_kernel(const PeakParams p) 
 // origin 0, mode 'reflect' inside the frame's own signal) into a shared row, (2) per band the minimum over the
 // bins [lo, hi) the band touches plus one bin either side, (3) odf = sum_b diff[b] * mask[b].
 // madmom/features/onsets.py:282-317.
+// One warp per frame, CTAs stride over the rows.  Per frame: (1) temporal maximum of the three neighbouring lgd
+// rows into a shared-memory row, coalesced; (2) band minima: every band's bin range is cut into pieces of kCfPiece
+// bins (table built once per CTA), one piece per lane and pass, combined with an integer atomicMin in shared memory
+// (the values are non-negative floats, so their bit patterns order like integers); (3) sum_b diff[b] * min[b].
+constexpr int kCfPiece = 8;
+constexpr int kCfMaxPieces = 1024;
+
 __global__ void __launch_bounds__(256) complex_flux_kernel(const float* __restrict__ lgd, int64_t ld_lgd,
                                                            const float* __restrict__ diff, int64_t ld_diff,
                                                            const int32_t* __restrict__ band_lo,
@@ -191,44 +198,97 @@ __global__ void __launch_bounds__(256) complex_flux_kernel(const float* __restri
                                                            int32_t n_bins, int64_t rows, int64_t seg_rows,
                                                            const int64_t* __restrict__ seg, int32_t n_seg, int32_t tf,
                                                            float* __restrict__ odf) {
-  extern __shared__ float s_rows[];                       // [warps][n_bins]
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
-  if (row >= rows) return;
-  int64_t s0 = 0, len = rows;
-  if (seg) {
-    const int s = find_segment(seg, n_seg, row);
-    s0 = seg[s]; len = seg[s + 1] - s0;
-  } else if (seg_rows > 0) {
-    s0 = (row / seg_rows) * seg_rows; len = seg_rows;
-  }
-  const int64_t t = row - s0;
-  float* mx = s_rows + (size_t)warp * n_bins;
-  const int half = tf / 2;
-  for (int k = lane; k < n_bins; k += 32) {
-    float m = lgd[row * ld_lgd + k];
-    for (int j = -half; j <= half; ++j) {
-      if (j == 0 || tf <= 1) continue;
-      int64_t q = t + j;
-      if (q < 0) q = -q - 1;                             // 'reflect': (b a | a b c)
-      if (q >= len) q = 2 * len - q - 1;
-      q = q < 0 ? 0 : (q >= len ? len - 1 : q);
-      m = fmaxf(m, lgd[(s0 + q) * ld_lgd + k]);
+  extern __shared__ float s_dyn[];                        // [warps][n_bins] rows, [warps][n_bands] minima, tables
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  float* s_rows = s_dyn;
+  int* s_min = reinterpret_cast<int*>(s_rows + (size_t)warps * n_bins);
+  int* s_lo = s_min + warps * n_bands;
+  int* s_hi = s_lo + n_bands;
+  int* s_off = s_hi + n_bands;                            // [n_bands + 1] first piece of each band
+  int* s_piece = s_off + n_bands + 1;                     // [kCfMaxPieces] band | piece index << 16
+  for (int b = threadIdx.x; b < n_bands; b += blockDim.x) { s_lo[b] = band_lo[b]; s_hi[b] = band_hi[b]; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int o = 0;
+    for (int b = 0; b < n_bands; ++b) {
+      s_off[b] = o;
+      const int len = s_hi[b] - s_lo[b];
+      o += len > 0 ? (len + kCfPiece - 1) / kCfPiece : 0;
     }
-    mx[k] = m;
+    s_off[n_bands] = o;
   }
-  __syncwarp();
-  float sum = 0.0f;
-  for (int b = lane; b < n_bands; b += 32) {
-    const int lo = band_lo[b], hi = band_hi[b];
-    float mn = INFINITY;
-    for (int k = lo; k < hi; ++k) mn = fminf(mn, mx[k]);
-    if (hi <= lo) mn = 0.0f;
-    sum += diff[row * ld_diff + b] * mn;
-  }
+  __syncthreads();
+  // band layouts with more pieces than the table holds (heavily overlapping bands) take the serial path below
+  const bool piecewise = s_off[n_bands] <= kCfMaxPieces && n_bands <= 0xffff;
+  const int n_pieces = piecewise ? s_off[n_bands] : 0;
+  if (piecewise)
+    for (int b = threadIdx.x; b < n_bands; b += blockDim.x)
+      for (int j = 0; j < s_off[b + 1] - s_off[b]; ++j) s_piece[s_off[b] + j] = b | (j << 16);
+  __syncthreads();
+
+  float* mx = s_rows + (size_t)warp * n_bins;
+  int* mn = s_min + warp * n_bands;
+  const int half = tf / 2;
+  for (int64_t row = (int64_t)blockIdx.x * warps + warp; row < rows; row += (int64_t)gridDim.x * warps) {
+    int64_t s0 = 0, len = rows;
+    if (seg) {
+      const int s = find_segment(seg, n_seg, row);
+      s0 = seg[s]; len = seg[s + 1] - s0;
+    } else if (seg_rows > 0) {
+      s0 = (row / seg_rows) * seg_rows; len = seg_rows;
+    }
+    const int64_t t = row - s0;
+    // rows of the temporal neighbourhood ('reflect': (b a | a b c))
+    int64_t q_prev = t - 1, q_next = t + 1;
+    if (q_prev < 0) q_prev = -q_prev - 1;
+    if (q_next >= len) q_next = 2 * len - q_next - 1;
+    q_prev = q_prev < 0 ? 0 : (q_prev >= len ? len - 1 : q_prev);
+    q_next = q_next < 0 ? 0 : (q_next >= len ? len - 1 : q_next);
+    const float* r0 = lgd + row * ld_lgd;
+    if (tf == 3) {
+      const float* ra = lgd + (s0 + q_prev) * ld_lgd;
+      const float* rb = lgd + (s0 + q_next) * ld_lgd;
+      for (int k = lane; k < n_bins; k += 32) mx[k] = fmaxf(fmaxf(ra[k], r0[k]), rb[k]);
+    } else {
+      for (int k = lane; k < n_bins; k += 32) {
+        float m = r0[k];
+        for (int j = -half; j <= half; ++j) {
+          if (j == 0 || tf <= 1) continue;
+          int64_t q = t + j;
+          if (q < 0) q = -q - 1;
+          if (q >= len) q = 2 * len - q - 1;
+          q = q < 0 ? 0 : (q >= len ? len - 1 : q);
+          m = fmaxf(m, lgd[(s0 + q) * ld_lgd + k]);
+        }
+        mx[k] = m;
+      }
+    }
+    for (int b = lane; b < n_bands; b += 32) mn[b] = 0x7f800000;        // +inf
+    __syncwarp();
+    for (int pi = lane; pi < n_pieces; pi += 32) {
+      const int code = s_piece[pi], b = code & 0xffff, j = code >> 16;
+      const int lo = s_lo[b] + j * kCfPiece, hi = min(lo + kCfPiece, s_hi[b]);
+      float m = mx[lo];
+      for (int k = lo + 1; k < hi; ++k) m = fminf(m, mx[k]);
+      atomicMin(&mn[b], __float_as_int(m));
+    }
+    if (!piecewise)
+      for (int b = lane; b < n_bands; b += 32) {
+        float m = INFINITY;
+        for (int k = s_lo[b]; k < s_hi[b]; ++k) m = fminf(m, mx[k]);
+        mn[b] = __float_as_int(m);
+      }
+    __syncwarp();
+    float sum = 0.0f;
+    for (int b = lane; b < n_bands; b += 32) {
+      const float m = s_hi[b] > s_lo[b] ? __int_as_float(mn[b]) : 0.0f;
+      sum += diff[row * ld_diff + b] * m;
+    }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-  if (lane == 0) odf[row] = sum;
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) odf[row] = sum;
+    __syncwarp();                                          // the row buffers are reused by the next frame
+  }
 }
 
 // ---------------------------------------------------------------------------------------------- spectral ODFs
@@ -413,11 +473,16 @@ extern "C" MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, co
     return MMB_E_INVALID;
   if (rows == 0) return MMB_OK;
   const int warps = 8;
-  const size_t smem = (size_t)warps * n_bins * sizeof(float);
+  const size_t smem = ((size_t)warps * n_bins + (size_t)warps * n_bands + 3 * (size_t)n_bands + 1 + kCfMaxPieces) *
+                      sizeof(float);
   if (smem > 48 * 1024 &&
       cudaFuncSetAttribute(complex_flux_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
     return MMB_E_CUDA;
-  const int64_t grid = (rows + warps - 1) / warps;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int64_t grid = (rows + warps - 1) / warps;
+  if (grid > (int64_t)sms * 4) grid = (int64_t)sms * 4;       // persistent CTAs, a multiple of the SM count
   complex_flux_kernel<<<(unsigned)grid, warps * 32, smem, (cudaStream_t)stream>>>(
       lgd_dev, ld_lgd, diff_dev, ld_diff, band_lo_dev, band_hi_dev, n_bands, n_bins, rows, rows_per_signal,
       seg_offsets_dev, n_segments, temporal_filter, odf_dev);

@@ -493,6 +493,8 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
     if (hptr[k] && hld[k] < width[k]) return fail(MMB_E_INVALID, "leading dimension smaller than the row width");
 
   // the plan's own pipeline buffers when no other thread is using them, else temporary ones
+  int64_t group_bytes = kGroupBytes;
+  if (const char* env = std::getenv("MMB_HOST_GROUP_MB")) group_bytes = std::max(1, std::atoi(env)) * (1ll << 20);
   Slot local[kSlots];
   std::unique_lock<std::mutex> lock(p->pipe->mu, std::try_to_lock);
   Slot* slots = lock.owns_lock() ? p->pipe->slots : local;
@@ -518,7 +520,7 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
       while (i1 < n) {
         const int64_t e1 = units[i1].pcm_offset + units[i1].pcm_len;
         const int64_t np1 = e1 > pcm1 ? e1 : pcm1;
-        if (i1 > i0 && (np1 - pcm0) * (int64_t)sb > kGroupBytes) break;
+        if (i1 > i0 && (np1 - pcm0) * (int64_t)sb > group_bytes) break;
         pcm1 = np1; ++i1;
       }
       const int64_t row0 = units[i0].out_row;

@@ -9,14 +9,17 @@
 //
 // Work decomposition
 //   unit   = track (or frame range of a long signal), split into chunks of `chunk_frames` output frames
-//   CTA    = persistent (one per SM), strides over chunks; a chunk is walked in rounds of FPR consecutive frames
-//   round  = the PCM span of the round is staged into one of two shared-memory buffers by ONE cp.async.bulk
-//            (TMA bulk copy, mbarrier completion) issued a full round ahead; spans that touch the edge of a
-//            signal are filled by the threads with zero padding instead
+//   CTA    = persistent (one per SM); its warps form one group (or several independent ones, group_warps) that
+//            strides over chunks and walks a chunk in rounds of FPR consecutive frames
+//   round  = the PCM span of the round sits in the group's staging buffer, put there by ONE cp.async.bulk (TMA bulk
+//            copy, mbarrier completion) that the last warp to have read the previous span issued; spans that touch
+//            the edge of a signal are filled by the threads with zero padding instead
 //   warp   = owns one frame per round (two for N = 1024) end to end: register-resident 32x32 FFT
 //            (fft_core.cuh) -> magnitudes in its scratch -> its own filterbank pass (FbPass schedule) -> log ->
-//            one row of the CTA's log-spectrogram ring
-//   barrier= ONE __syncthreads per round, between "rows written" and "lagged difference read"
+//            one row of the group's log-spectrogram ring
+//   sync   = no CTA barrier in the steady state: an mbarrier counts the rows of a round; a warp waits for it only
+//            when it is about to write its row of the NEXT round and then does the lagged difference, flux and
+//            output stores of the previous one (warps drift by up to one round)
 // A chunk recomputes its `diff_frames` lead-in frames instead of exchanging them with its neighbour.
 #include "frame_fft.cuh"
 #include "frontend_params.h"

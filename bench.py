@@ -293,7 +293,7 @@ def run_ours(args):
     fp32_peak = _lib.measure_fp32_peak(local)
     ach_gbs = frames_per_step * bytes_per_frame / (float(np.mean(step_ms)) * 1e-3) / 1e9
     ach_tf = frames_per_step * fpf / (float(np.mean(step_ms)) * 1e-3) / 1e12
-    traffic = None
+    traffic = counts = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
@@ -301,6 +301,7 @@ def run_ours(args):
                 t = json.load(f).get(args.workload)
             # measured DRAM bytes per frame (ncu --set full of the same command) x frames of one launch
             traffic = float(t["dram_bytes_per_frame"]) * frames_per_step / len(recipes) if t else None
+            counts = t if t and "warp_instructions_per_frame" in t else None
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
@@ -310,6 +311,20 @@ def run_ours(args):
                 "fp32": {"binding": True, "achieved": ach_tf, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": ach_tf / fp32_peak if fp32_peak else None, "flops_per_frame": fpf,
                          "peak_source": "measured (mmb_measure_fp32_peak, dependent FFMA chains, best of 5)"}}
+
+    if counts and clocks.get("sm_mhz"):
+        # the ceilings that actually bind (DESIGN.md "Which roof binds"): 4 warp-instructions and 1 shared-memory
+        # wavefront per clock and SM (measured, mmb_rate_probe); counts per frame from the committed ncu capture,
+        # time and clock from this run
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        clk_per_frame = launch_ms * 1e-3 * clocks["sm_mhz"] * 1e6 * sms / (frames_per_step / len(recipes))
+        roofline["sm"] = {
+            "sm_clocks_per_frame": clk_per_frame,
+            "issue_slots": {"per_frame": counts["warp_instructions_per_frame"], "peak_per_clk_sm": 4.0,
+                            "frac": counts["warp_instructions_per_frame"] / 4.0 / clk_per_frame},
+            "shared_pipe": {"per_frame": counts["shared_wavefronts_per_frame"], "peak_per_clk_sm": 1.0,
+                            "frac": counts["shared_wavefronts_per_frame"] / clk_per_frame},
+            "counts_source": counts.get("counts_source")}
 
     cpu = None
     if world == 1 and not args.no_cpu:

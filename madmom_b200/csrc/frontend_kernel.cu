@@ -372,11 +372,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
       }
       group_sync(grp, gthreads);
     }
-    const long long g0 = D->g0, ga = D->ga, row0 = D->row0, s_begin = D->s_begin;
     const S* span0 = buf + D->shift;
-    const int slot0 = D->slot0;
 
     // ================= this warp's frame(s): FFT -> magnitudes -> filterbank -> [phase C of round r-1] -> ring row
+    // The round descriptor is read again after the FFT instead of keeping its 64-bit fields in registers across it.
     float2 v[32];
     if (N == 1024) {
       const int fa = 2 * gwarp, fb = 2 * gwarp + 1;
@@ -384,11 +383,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
         if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
       } else {
-        const long long gA = g0 + fa, gB = g0 + fb;
         const bool haveB = fb < nfr;
-        const S* xa = span0 + (int)(frame_start_sample(gA, p.hop, N, p.origin) - s_begin);
-        const S* xb = haveB ? span0 + (int)(frame_start_sample(gB, p.hop, N, p.origin) - s_begin) : nullptr;
-        load_frames_1024<S>(lane, v, xa, xb, s_win);
+        {
+          const long long gA = D->g0 + fa, s_begin = D->s_begin;
+          const S* xa = span0 + (int)(frame_start_sample(gA, p.hop, N, p.origin) - s_begin);
+          const S* xb = haveB ? span0 + (int)(frame_start_sample(gA + 1, p.hop, N, p.origin) - s_begin) : nullptr;
+          load_frames_1024<S>(lane, v, xa, xb, s_win);
+        }
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
         core_pass1(lane, v, ex, s_tw1);
         __syncwarp();
@@ -397,23 +398,26 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         core_pass2_fft(v);
         core_publish_upper(lane, v, ex, true);
         __syncwarp();
-        BinSink oa, ob;
-        const long long rowA = row0 + gA, rowB = rowA + 1;
-        oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
-        oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
-        oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
-        ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
-        oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
-        ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
-        if (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row) split_1024x2(lane, v, ex, oa, ob, haveB);
-        else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
+        const long long gA = D->g0 + fa, gB = gA + 1, ga = D->ga;
+        const long long rowA = D->row0 + gA, rowB = rowA + 1;
+        {
+          BinSink oa, ob;
+          oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
+          oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
+          oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
+          ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
+          oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
+          ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
+          if (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row) split_1024x2(lane, v, ex, oa, ob, haveB);
+          else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
+        }
         if (nb > 0) {
           __syncwarp();
           if (!haveB) for (int i = lane; i < 512; i += 32) my_mag[512 + i] = 0.0f;
           __syncwarp();
           warp_filterbank<2>(p, lane, my_mag, my_mag + 512, my_part, s_pass, s_w, s_start, s_pid);
           MMB_PENDING_DIFFERENCE();
-          int sa = slot0 + fa; if (sa >= R) sa -= R;
+          int sa = D->slot0 + fa; if (sa >= R) sa -= R;
           warp_band_epilogue(p, lane, my_part, s_ring + sa * nb, rowA, gA >= ga);
           if (haveB) {
             int sb = sa + 1; if (sb >= R) sb -= R;
@@ -426,13 +430,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
       frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
       if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
     } else {
-      const long long g = g0 + gwarp;
-      const S* x = span0 + (int)(frame_start_sample(g, p.hop, N, p.origin) - s_begin);
-      BinSink o;
-      const long long row = row0 + g;
-      o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
-      o.stft_row = (p.out_stft && g >= ga) ? p.out_stft + row * p.ld_stft : nullptr;
-      o.spec_row = (p.out_spec && g >= ga) ? p.out_spec + row * p.ld_spec : nullptr;
+      const S* x = span0 + (int)(frame_start_sample(D->g0 + gwarp, p.hop, N, p.origin) - D->s_begin);
       if (N == 2048) {
         load_frame_2048<S>(lane, v, x, s_win);
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
@@ -443,7 +441,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         core_pass2_fft(v);
         core_publish_upper(lane, v, ex, true);
         __syncwarp();
-        if (p.out_lgd && g >= ga) {
+        const long long g = D->g0 + gwarp, row = D->row0 + g;
+        const bool emit = g >= D->ga;
+        BinSink o;
+        o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
+        o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
+        o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
+        if (p.out_lgd && emit) {
           split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
         } else if (o.stft_row || o.spec_row) {
           split_2048(lane, v, ex, s_tw2k, o);
@@ -462,6 +466,12 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           core_pass2_fft(v);
           core_publish_upper(lane, v, ex, c == 0);
           __syncwarp();
+          const long long g = D->g0 + gwarp, row = D->row0 + g;
+          const bool emit = g >= D->ga;
+          BinSink o;
+          o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
+          o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
+          o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
           o.mag = c == 0 ? my_mag_even : my_mag;
           if (o.stft_row || o.spec_row) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
           else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
@@ -473,8 +483,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         if (N == 4096) warp_filterbank<1, true>(p, lane, my_mag_even, my_mag, my_part, s_pass, s_w, s_start, s_pid);
         else warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
         MMB_PENDING_DIFFERENCE();
-        int sl = slot0 + gwarp; if (sl >= R) sl -= R;
-        warp_band_epilogue(p, lane, my_part, s_ring + sl * nb, row, g >= ga);
+        const long long g = D->g0 + gwarp;
+        int sl = D->slot0 + gwarp; if (sl >= R) sl -= R;
+        warp_band_epilogue(p, lane, my_part, s_ring + sl * nb, D->row0 + g, g >= D->ga);
         MMB_ROWS_WRITTEN();
       }
     }

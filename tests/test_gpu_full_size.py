@@ -1,0 +1,81 @@
+"""BASELINE.json configurations at their full size (1024 tracks x 30 s per GPU), checked through properties that do
+not need the CPU oracle on all of it: per-track results are independent of batching, chunking and launch, the flux is
+the row sum of the difference, lead-in rows are zero, runs are bit-reproducible; a few tracks are also compared with
+the oracle."""
+import numpy as np
+import pytest
+
+from conftest import assert_close
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+TRACKS, SECONDS = 1024, 30.0
+
+
+@pytest.fixture(scope="module")
+def batch():
+    from madmom_b200.synth import make_batch_torch
+    pcm = make_batch_torch(TRACKS, SECONDS, device="cuda", seed=1000)
+    return pcm, [pcm.shape[1]] * TRACKS
+
+
+def test_config2_logfiltspecflux_full_size(batch):
+    from oracle import frontend as O
+    from madmom_b200 import recipe as R
+    from madmom_b200.batch import BatchFrontEnd
+    pcm, lengths = batch
+    fe = BatchFrontEnd(R.LOGFILTSPECFLUX)
+    out = fe.run_device(pcm, lengths, ("diff", "odf"))
+    diff, odf = out["diff"], out["odf"]
+    T = R.num_frames(lengths[0], 441.)
+    assert T == 3000 and diff.shape == (TRACKS * T, 81) and odf.shape == (TRACKS * T,)
+    assert bool(torch.isfinite(diff).all()) and float(diff.min()) >= 0.0
+    d = fe.plans[0].diff_frames
+    lead = diff.view(TRACKS, T, 81)[:, :d]
+    assert not bool(lead.any())                                   # first d rows of every track (spectrogram.py:984-989)
+    # flux = row sum (features/onsets.py:163-190); the kernel adds 3 values per lane and then a shuffle tree
+    ref_sum = diff.double().sum(dim=1)
+    assert float((odf.double() - ref_sum).abs().max()) <= 1e-5 * max(1.0, float(ref_sum.max()))
+    # bit-reproducible
+    again = fe.run_device(pcm, lengths, ("diff", "odf"))
+    assert torch.equal(again["diff"], diff) and torch.equal(again["odf"], odf)
+    # independent of batching: tracks on their own, and a different chunk size, give the same bits
+    rng = np.random.default_rng(0)
+    picks = sorted(set([0, TRACKS - 1] + list(rng.integers(0, TRACKS, 6))))
+    small = BatchFrontEnd(R.LOGFILTSPECFLUX, chunk_frames=97)
+    for i in picks:
+        alone = fe.run_device(pcm[i], [lengths[i]], ("diff",))["diff"]
+        assert torch.equal(alone, diff[i * T:(i + 1) * T]), i
+        assert torch.equal(small.run_device(pcm[i], [lengths[i]], ("diff",))["diff"], alone), i
+    # against the oracle (two tracks)
+    for i in picks[:2]:
+        x = pcm[i].cpu().numpy()
+        st = O.run_recipe(x, dict(frame_size=2048, hop_size=441., num_bands=12, norm_filters=False, mul=1, add=1,
+                                  diff_ratio=0.5, positive_diffs=True), stages=True)
+        assert_close(diff[i * T:(i + 1) * T].cpu().numpy(), st["diff"], what="config 2 diff, track %d" % i)
+        assert_close(odf[i * T:(i + 1) * T].cpu().numpy(), st["odf"], what="config 2 flux, track %d" % i)
+
+
+def test_config3_multires_full_size(batch):
+    from madmom_b200 import recipe as R
+    from madmom_b200.batch import BatchFrontEnd
+    pcm, lengths = batch
+    fe = BatchFrontEnd(R.RNN_BEAT)
+    stack = fe.run_device(pcm, lengths, ("stack",))["stack"]
+    T = 3000
+    assert stack.shape == (TRACKS * T, 266) and bool(torch.isfinite(stack).all())
+    # column blocks: [log 39 | diff 39 | log 45 | diff 45 | log 49 | diff 49]; each block equals the single-recipe run
+    c = 0
+    for rec, plan in zip(R.RNN_BEAT, fe.plans):
+        b = plan.num_bands
+        one = BatchFrontEnd([rec]).run_device(pcm[:64], lengths[:64], ("log", "diff"))
+        assert torch.equal(one["log"], stack[:64 * T, c:c + b])
+        assert torch.equal(one["diff"], stack[:64 * T, c + b:c + 2 * b])
+        c += 2 * b
+    assert c == 266
+    picks = [3, 700]
+    for i in picks:
+        alone = fe.run_device(pcm[i], [lengths[i]], ("stack",))["stack"]
+        assert torch.equal(alone, stack[i * T:(i + 1) * T]), i

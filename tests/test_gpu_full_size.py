@@ -79,3 +79,66 @@ def test_config3_multires_full_size(batch):
     for i in picks:
         alone = fe.run_device(pcm[i], [lengths[i]], ("stack",))["stack"]
         assert torch.equal(alone, stack[i * T:(i + 1) * T]), i
+
+
+def test_config4_ten_hour_signal_shards():
+    """One 10-hour signal (1 587 600 000 samples): the frame ranges of 8 ranks, run one after the other on this GPU
+    and concatenated like the all-gather does, are bit-identical to the single launch over the whole signal; shard
+    boundaries are additionally compared with the oracle on their PCM neighbourhood."""
+    from oracle import frontend as O
+    from madmom_b200 import parallel, recipe as R
+    from madmom_b200.batch import BatchFrontEnd
+    from madmom_b200.synth import make_batch_torch
+    n = 10 * 3600 * 44100
+    x = make_batch_torch(1, n / 44100.0, device="cuda", seed=7).reshape(-1)
+    assert x.numel() == n
+    rec = R.SUPERFLUX
+    whole = BatchFrontEnd(rec).run_device(x, [n], ("diff",))["diff"]
+    T = R.num_frames(n, rec.hop_size)
+    assert whole.shape == (T, 140) and T == 3600000
+    fe = parallel.LongSignalFrontEnd(rec)
+    world = 8
+    r0 = 0
+    for rank in range(world):
+        sh = fe.shard(n, world, rank)
+        local = fe.run_local(x[sh.sample_lo:sh.sample_hi].contiguous(), sh, ("diff",))["diff"]
+        rows = min(local.shape[0], T - r0)
+        assert torch.equal(local[:rows], whole[r0:r0 + rows]), rank
+        r0 += rows
+    assert r0 == T
+    # oracle on the neighbourhood of two shard boundaries (frames [f - 3, f + 3))
+    d = fe.plan.diff_frames
+    for f in (T // 8, 5 * (T // 8)):
+        lo = max(O.frame_start(f - 3 - d, 2048, 441.), 0)
+        hi = O.frame_start(f + 3, 2048, 441.) + 2048
+        seg = x[lo:hi].cpu().numpy()
+        # frames f-3-d .. f+2 cut out of the segment with their global start samples
+        fr = np.stack([seg[O.frame_start(g, 2048, 441.) - lo:O.frame_start(g, 2048, 441.) - lo + 2048]
+                       for g in range(f - 3 - d, f + 3)])
+        win = O.fft_window(np.hanning, 2048, np.int16)
+        spec = O.spec(O.stft(fr, win))
+        fb = O.logarithmic_filterbank(O.fft_frequencies(1024, 44100), num_bands=24, norm_filters=False)
+        logf = O.logarithmic(O.filtered(spec, fb))
+        want = O.difference(logf, d, 3, True)[d:]
+        assert_close(whole[f - 3:f + 3].cpu().numpy(), want, what="config 4 boundary %d" % f)
+
+
+def test_config5_complexflux_full_size(batch):
+    from oracle import frontend as O
+    from madmom_b200 import recipe as R
+    from madmom_b200.batch import BatchFrontEnd, complex_flux_batch
+    pcm, lengths = batch
+    fe = BatchFrontEnd([R.COMPLEXFLUX])
+    odf = complex_flux_batch(fe, pcm, lengths)
+    T = R.num_frames(lengths[0], R.COMPLEXFLUX.hop_size)
+    assert T == 6000 and odf.shape == (TRACKS * T,) and bool(torch.isfinite(odf).all())
+    assert torch.equal(complex_flux_batch(fe, pcm, lengths), odf)                     # reproducible
+    # independent of the grouping of tracks into scratch-sized launches
+    assert torch.equal(complex_flux_batch(fe, pcm, lengths, scratch_bytes=300 << 20), odf)
+    for i in (0, 517):
+        alone = complex_flux_batch(fe, pcm[i], [lengths[i]])
+        assert torch.equal(alone, odf[i * T:(i + 1) * T]), i
+    i = 517
+    st = O.run_recipe(pcm[i].cpu().numpy(), dict(O.SUPERFLUX_200, circular_shift=True), stages=True)
+    want = O.complex_flux(st["log"], st["stft"], st["filterbank"], st["diff_frames"])
+    assert_close(odf[i * T:(i + 1) * T].cpu().numpy(), want, what="config 5 ODF")

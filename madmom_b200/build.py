@@ -16,6 +16,10 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 
 
+if os.environ.get("MMB_NVCC_EXTRA"):              # experiments only, e.g. "-Xptxas -O2"
+    NVCC_FLAGS = NVCC_FLAGS + os.environ["MMB_NVCC_EXTRA"].split()
+
+
 def _nvcc():
     for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
         if cand and (os.path.isabs(cand) and os.path.exists(cand) or not os.path.isabs(cand)):

@@ -16,7 +16,7 @@ def _build(tmp_path):
     if not os.path.exists(os.path.join(LIB_DIR, "libmadmom_b200.so")):
         sys.path.insert(0, ROOT)
         from madmom_b200 import build
-        build.build()
+        build.build_library()
     exe = str(tmp_path / "c_abi_example")
     cmd = ["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-O1", SRC, "-o", exe, "-L" + LIB_DIR,
            "-lmadmom_b200", "-Wl,-rpath," + LIB_DIR]

@@ -197,7 +197,10 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: madmom_b200 has no CPU path")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_bound = False
     if world > 1:
+        from madmom_b200 import parallel
+        numa_bound = parallel.bind_host_thread_to_gpu(local) if os.environ.get("MMB_NO_NUMA_BIND") is None else False
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -338,7 +341,8 @@ def run_ours(args):
                        "sample_rate": SR, "pcm": "int16", "frames_per_step_per_gpu": frames_per_step,
                        "outputs": {k: list(v.shape) for k, v in out.items()},
                        "l2": "inputs (%.2f GB PCM per step) larger than L2" % (pcm.numel() * 2 / 1e9),
-                       "parallelism": "tracks sharded over %d GPU(s), no collective" % world},
+                       "parallelism": "tracks sharded over %d GPU(s), no collective" % world,
+                       "host_numa_bound": numa_bound},
             "e2e": e2e,
             "gpu_launches": gpu_launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line))

@@ -20,6 +20,20 @@ import numpy as np
 from . import recipe as R
 
 
+def bind_host_thread_to_gpu(device):
+    """Pin the calling host thread to the CPUs next to GPU `device` (NVML's ideal affinity), so that the pinned
+    staging buffers allocated afterwards and the copy threads sit on the GPU's NUMA node.  With one process per GPU
+    on a two-socket host the PCIe transfers of the host path otherwise cross the socket interconnect.  Returns True
+    when the affinity was set."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(int(device)))
+        return True
+    except Exception:
+        return False
+
+
 def shard_tracks(n_tracks, world_size, rank):
     """Contiguous block [lo, hi) of tracks for `rank`; blocks differ by at most one track."""
     base, extra = divmod(int(n_tracks), int(world_size))

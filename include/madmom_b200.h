@@ -205,7 +205,8 @@ MMB_API int mmb_spectral_odf(int32_t mode, const void* stft_dev, int64_t ld_stft
 MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops);
 
 /* Instruction-rate probes behind the issue-slot roofline in DESIGN.md: which = 1 FFMA with three register
- * operands, 2 FADD, 3 FMUL+FADD pairs, 4 LDS.64 + 2 FFMA.  *ginst_per_s = 1e9 thread-level FP instructions
+ * operands, 2 FADD, 3 FMUL+FADD pairs, 4 LDS.64 + 2 FFMA, 5 LDS.32, 6 SHFL, 7 LDS.32 + SHFL, 8 FADD2 (f32x2),
+ * 9 FFMA2 (f32x2), 10 FFMA2 + LDS.32 + FADD.  *ginst_per_s = 1e9 thread-level FP instructions
  * per second over the whole device. */
 MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s);
 

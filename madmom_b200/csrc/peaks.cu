@@ -80,6 +80,15 @@ __global__ void __launch_bounds__(256) rate_probe(float* out, int iters, float a
         acc[i] += reinterpret_cast<const float*>(sm)[(threadIdx.x + 32 * i + it) & 1023];
       } else if (WHICH == 6) {           // SHFL only
         acc[i] = __shfl_sync(0xffffffffu, acc[i], (threadIdx.x + i + 1) & 31) + x[i];
+      } else if (WHICH == 8 || WHICH == 9 || WHICH == 10) {
+        // packed FP32 pairs (sm_100 add/fma.rn.f32x2 -> FADD2 / FFMA2): two lanes of work per instruction
+        unsigned long long p, q, r;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(p) : "f"(acc[i]), "f"(y[i]));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(q) : "f"(x[i]), "f"(x[(i + 1) % ILP]));
+        if (WHICH == 8) asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(p), "l"(q));
+        else asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(p), "l"(q), "l"(q));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[i]), "=f"(y[i]) : "l"(r));
+        if (WHICH == 10) acc[i] += reinterpret_cast<const float*>(sm)[(threadIdx.x + 32 * i + it) & 1023];
       } else if (WHICH == 7) {           // one LDS.32 + one SHFL per step
         acc[i] = __shfl_sync(0xffffffffu, acc[i], (threadIdx.x + i + 1) & 31) +
                  reinterpret_cast<const float*>(sm)[(threadIdx.x + 32 * i + it) & 1023];
@@ -96,7 +105,7 @@ __global__ void __launch_bounds__(256) rate_probe(float* out, int iters, float a
 // result: warp-level FP instructions per clock per SM at the current clock estimate is left to the caller;
 // *ginst_per_s receives 1e9 thread-level FP instructions per second (whole device).
 extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s) {
-  if (!ginst_per_s || which < 1 || which > 7) return MMB_E_INVALID;
+  if (!ginst_per_s || which < 1 || which > 10) return MMB_E_INVALID;
   if (cudaSetDevice(device) != cudaSuccess) return MMB_E_CUDA;
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return MMB_E_CUDA;
@@ -114,7 +123,10 @@ extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* gin
     else if (which == 4) rate_probe<4><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     else if (which == 5) rate_probe<5><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     else if (which == 6) rate_probe<6><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
-    else rate_probe<7><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 7) rate_probe<7><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 8) rate_probe<8><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 9) rate_probe<9><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else rate_probe<10><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     cudaEventRecord(e1);
     if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return MMB_E_CUDA; }
     float ms = 0.f;

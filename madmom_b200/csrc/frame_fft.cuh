@@ -35,7 +35,7 @@ MMB_HD void load_frame_2048(int lane, float2 (&v)[32], const S* x, const float* 
   for (int m = 0; m < 32; ++m) {
     const int n = lane + 32 * m;
     const float2 w = *reinterpret_cast<const float2*>(win + 2 * n);
-    v[m] = make_float2(to_f32(x[2 * n]) * w.x, to_f32(x[2 * n + 1]) * w.y);
+    v[m] = mul2(make_float2(to_f32(x[2 * n]), to_f32(x[2 * n + 1])), w);
   }
 }
 
@@ -59,12 +59,12 @@ MMB_HD void load_frame_4096(int lane, int c, float2 (&v)[32], const S* x, const 
     const int n = lane + 32 * m;
     const float2 w0 = *reinterpret_cast<const float2*>(win + 2 * n);
     const float2 w1 = *reinterpret_cast<const float2*>(win + 2 * n + 2048);
-    const float2 z0 = make_float2(to_f32(x[2 * n]) * w0.x, to_f32(x[2 * n + 1]) * w0.y);
-    const float2 z1 = make_float2(to_f32(x[2 * n + 2048]) * w1.x, to_f32(x[2 * n + 2049]) * w1.y);
+    const float2 z0 = mul2(make_float2(to_f32(x[2 * n]), to_f32(x[2 * n + 1])), w0);
+    const float2 z1 = mul2(make_float2(to_f32(x[2 * n + 2048]), to_f32(x[2 * n + 2049])), w1);
     if (c == 0) {
-      v[m] = make_float2(z0.x + z1.x, z0.y + z1.y);
+      v[m] = add2(z0, z1);
     } else {
-      v[m] = cmul(make_float2(z0.x - z1.x, z0.y - z1.y), tw2k[m * 32 + lane]);
+      v[m] = cmul(sub2(z0, z1), tw2k[m * 32 + lane]);
     }
   }
 }
@@ -123,8 +123,8 @@ MMB_HD void split_2048(int lane, const float2 (&v)[32], const float2* zs, const 
     const int k = lane + 32 * q, kp = 1024 - k;
     const float2 zp = zs[kp];
     const float2 w = tw2k[q * 32 + lane];
-    const float ar = zk.x + zp.x, ai = zk.y - zp.y;
-    const float br = zk.x - zp.x, bi = zk.y + zp.y;
+    const float2 sp = add2(zk, zp), sm = sub2(zk, zp);          // (ar, bi), (br, ai)
+    const float ar = sp.x, ai = sm.y, br = sm.x, bi = sp.y;
     const float tr = w.x * br - w.y * bi, ti = w.x * bi + w.y * br;
     out.put(k, ar + ti, ai - tr);
     if (kp < 1024) out.put(kp, ar - ti, -(ai + tr));
@@ -179,8 +179,8 @@ __device__ __forceinline__ void split_2048_lgd(int lane, const float2 (&v)[32], 
     const int k = lane + 32 * q, kp = 1024 - k;
     const float2 zp = zs[kp];
     const float2 w = tw2k[q * 32 + lane];
-    const float ar = zk.x + zp.x, ai = zk.y - zp.y;
-    const float br = zk.x - zp.x, bi = zk.y + zp.y;
+    const float2 sp = add2(zk, zp), sm = sub2(zk, zp);          // (ar, bi), (br, ai)
+    const float ar = sp.x, ai = sm.y, br = sm.x, bi = sp.y;
     const float tr = w.x * br - w.y * bi, ti = w.x * bi + w.y * br;
     const float2 xk = make_float2(ar + ti, ai - tr);
     const float2 xp = make_float2(ar - ti, -(ai + tr));                  // X[1024 - k]
@@ -208,8 +208,9 @@ MMB_HD void split_1024x2(int lane, const float2 (&v)[32], const float2* zs, cons
     const float2 zk = v[brev5(q)];
     const int k = lane + 32 * q;
     const float2 zp = zs[1024 - k];
-    outA.put(k, zk.x + zp.x, zk.y - zp.y);              // (Z[k] + conj Z[-k]) / 2
-    if (haveB) outB.put(k, zk.y + zp.y, zp.x - zk.x);   // (Z[k] - conj Z[-k]) / 2i
+    const float2 sp = add2(zk, zp), sm = sub2(zk, zp);
+    outA.put(k, sp.x, sm.y);                             // (Z[k] + conj Z[-k]) / 2
+    if (haveB) outB.put(k, sp.y, -sm.x);                 // (Z[k] - conj Z[-k]) / 2i
   }
 }
 
@@ -226,8 +227,8 @@ MMB_HD void split_4096(int lane, int c, const float2 (&v)[32], const float2* zs,
     const int jp = (c == 0) ? 1024 - j : 1023 - j;
     const float2 zp = zs[jp];
     const float2 w = (c == 0) ? tw2k[q * 32 + lane] : tw4k[q * 32 + lane];
-    const float ar = zk.x + zp.x, ai = zk.y - zp.y;
-    const float br = zk.x - zp.x, bi = zk.y + zp.y;
+    const float2 sp = add2(zk, zp), sm = sub2(zk, zp);          // (ar, bi), (br, ai)
+    const float ar = sp.x, ai = sm.y, br = sm.x, bi = sp.y;
     const float tr = w.x * br - w.y * bi, ti = w.x * bi + w.y * br;
     const int k = 2 * j + c, kp = 2 * jp + c;
     out.put_at(j, k, ar + ti, ai - tr);

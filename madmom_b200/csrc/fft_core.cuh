@@ -101,6 +101,21 @@ MMB_HD float2 mul2(float2 a, float2 b) {
 #endif
 }
 
+MMB_HD float2 fma2(float2 a, float2 b, float2 c) {      // a * b + c per half, each a fused multiply-add
+#if defined(__CUDA_ARCH__)
+  unsigned long long x, y, z, r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(x) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(y) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(z) : "f"(c.x), "f"(c.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(x), "l"(y), "l"(z));
+  float2 o;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(o.x), "=f"(o.y) : "l"(r));
+  return o;
+#else
+  return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+#endif
+}
+
 // One radix-2 DIF butterfly with twiddle W_32^(tw) = exp(-2 pi i tw / 32) on the difference output.
 template <int TW>
 MMB_HD void bfly(float2& u, float2& w) {

@@ -171,21 +171,24 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
     // SPLIT: taps 0, 2 read bins st, st + 2 (array of st's parity), taps 1, 3 the other array
     const float* m0 = SPLIT ? ((st & 1) ? mag1 + (st >> 1) : mag0 + (st >> 1)) : mag0 + st;
     const float* m1 = SPLIT ? ((st & 1) ? mag0 + ((st + 1) >> 1) : mag1 + (st >> 1)) : ((NF == 2) ? mag1 + st : mag0);
-    float a0 = 0.0f, a1 = 0.0f, c0 = 0.0f, c1 = 0.0f;    // even / odd taps, two frames
+    float2 acc0 = make_float2(0.0f, 0.0f), acc1 = make_float2(0.0f, 0.0f);    // (even taps, odd taps), two frames
 #pragma unroll 1
     for (int i = 0; i < fp.iters; i += 4) {          // pass lengths are multiples of four (capi.cu)
       const float4 wv = *w;                          // taps i .. i+3 of this lane
-      const float w0 = wv.x, w1 = wv.y, w2 = wv.z, w3 = wv.w;
+      const float2 w01 = make_float2(wv.x, wv.y), w23 = make_float2(wv.z, wv.w);
       const float x0 = m0[0], x1 = SPLIT ? m1[0] : m0[1], x2 = SPLIT ? m0[1] : m0[2], x3 = SPLIT ? m1[1] : m0[3];
-      a0 = fmaf(x0, w0, a0); c0 = fmaf(x1, w1, c0); a0 = fmaf(x2, w2, a0); c0 = fmaf(x3, w3, c0);
+      acc0 = fma2(make_float2(x0, x1), w01, acc0);   // packed pairs: same per-half FMA chains as the scalar form
+      acc0 = fma2(make_float2(x2, x3), w23, acc0);
       if (SPLIT) { m0 += 2; m1 += 2; w += 32; continue; }
       if (NF == 2) {
         const float y0 = m1[0], y1 = m1[1], y2 = m1[2], y3 = m1[3];
-        a1 = fmaf(y0, w0, a1); c1 = fmaf(y1, w1, c1); a1 = fmaf(y2, w2, a1); c1 = fmaf(y3, w3, c1);
+        acc1 = fma2(make_float2(y0, y1), w01, acc1);
+        acc1 = fma2(make_float2(y2, y3), w23, acc1);
         m1 += 4;
       }
       w += 32; m0 += 4;
     }
+    const float a0 = acc0.x, c0 = acc0.y, a1 = acc1.x, c1 = acc1.y;
     const int pid = s_pid[ps * 32 + lane];
     part[pid] = a0 + c0;
     if (NF == 2) part[np1 + pid] = a1 + c1;

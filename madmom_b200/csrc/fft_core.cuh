@@ -116,24 +116,22 @@ MMB_HD float2 fma2(float2 a, float2 b, float2 c) {      // a * b + c per half, e
 #endif
 }
 
-// One radix-2 DIF butterfly with twiddle W_32^(tw) = exp(-2 pi i tw / 32) on the difference output.
+// One radix-2 DIF butterfly with twiddle W_32^(tw) = exp(-2 pi i tw / 32) on the difference output:
+//   (dr + i di)(c - i s) = (dr c + di s) + i (di c - dr s)
+// as one packed multiply by the broadcast immediate c and two scalar FMAs with the immediate s.  (The fully
+// packed form, FFMA2 with a (s, -s) register pair, was measured slower: three register-pair operands.)
 template <int TW>
 MMB_HD void bfly(float2& u, float2& w) {
   const float2 sum = add2(u, w), dif = sub2(u, w);
-  const float dr = dif.x, di = dif.y;
   u = sum;
   if (TW == 0) {                       // * 1
-    w.x = dr; w.y = di;
+    w = dif;
   } else if (TW == 8) {                // * (-i)
-    w.x = di; w.y = -dr;
-  } else if (TW == 4) {                // * (1 - i) / sqrt2
-    w.x = (dr + di) * MMB_C32_4; w.y = (di - dr) * MMB_C32_4;
-  } else if (TW == 12) {               // * (-1 - i) / sqrt2
-    w.x = (di - dr) * MMB_C32_4; w.y = -(dr + di) * MMB_C32_4;
-  } else {                             // (dr + i di)(c - i s)
+    w = make_float2(dif.y, -dif.x);
+  } else {
     constexpr float c = cos32(TW), s = sin32(TW);
-    w.x = dr * c + di * s;
-    w.y = di * c - dr * s;
+    const float2 t = mul2(dif, make_float2(c, c));
+    w = make_float2(fmaf(dif.y, s, t.x), fmaf(-dif.x, s, t.y));
   }
 }
 

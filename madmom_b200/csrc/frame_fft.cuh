@@ -144,7 +144,9 @@ __device__ __forceinline__ float abs_angle_over_pi(float2 a, float2 b, float fli
   // 7-term minimax polynomial (3.2e-7 rad), then the reflections; 0 for the zero vector like np.angle
   const float ar = fabsf(re);
   const float mx = fmaxf(im, ar), mn = fminf(im, ar);
-  const float t = mx > 0.0f ? __fdividef(mn, mx) : 0.0f;
+  float rmx;                                            // the zero vector gives t = 0 (0 times a finite reciprocal)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rmx) : "f"(fmaxf(mx, 1e-30f)));
+  const float t = mn * rmx;
   const float u = t * t;
   float p = 0.00681148456f;
   p = fmaf(p, u, -0.0336031997f);

@@ -451,7 +451,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
         o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
         if (p.out_lgd && emit) {
-          split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
+          if (o.stft_row || o.spec_row) split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
+          else split_2048_lgd(lane, v, ex, s_tw2k, quiet(o), p.out_lgd + row * p.ld_lgd, sgn_odd);
         } else if (o.stft_row || o.spec_row) {
           split_2048(lane, v, ex, s_tw2k, o);
         } else {

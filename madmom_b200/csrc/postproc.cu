@@ -14,6 +14,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/madmom_b200.h"
 #include "frontend_params.h"
@@ -282,12 +283,108 @@ __global__ void __launch_bounds__(256) complex_flux_kernel(const float* __restri
     float sum = 0.0f;
     for (int b = lane; b < n_bands; b += 32) {
       const float m = s_hi[b] > s_lo[b] ? __int_as_float(mn[b]) : 0.0f;
-      sum += diff[row * ld_diff + b] * m;
+      sum = __fmaf_rn(diff[row * ld_diff + b], m, sum);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     if (lane == 0) odf[row] = sum;
     __syncwarp();                                          // the row buffers are reused by the next frame
+  }
+}
+
+// Streaming variant for temporal_filter = 3 and n_bins = 128 NV: a warp walks a contiguous run of rows and keeps
+// the previous, the current and the next lgd row in registers (float4 chunks, NV per lane), so every row is read
+// from HBM once instead of three times, with the row after next already in flight while the band minima of the
+// current row are taken.  The temporal maximum goes to a shared-memory row; lane l owns the bands l, l + 32, ...
+// and walks their bin ranges itself (neighbouring bands have similar widths, so the uniform trip count of a
+// group of 32 bands wastes little), which needs no atomics and no table of minima.
+template <int NV>
+__device__ __forceinline__ void cf_load_row(float4 (&r)[NV], const float* __restrict__ row, int lane) {
+  const float4* p = reinterpret_cast<const float4*>(row);
+#pragma unroll
+  for (int j = 0; j < NV; ++j) r[j] = __ldg(p + lane + 32 * j);
+}
+__device__ __forceinline__ float4 fmax4(float4 a, float4 b) {
+  return make_float4(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z), fmaxf(a.w, b.w));
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256, 2) complex_flux_stream_kernel(
+    const float* __restrict__ lgd, int64_t ld_lgd, const float* __restrict__ diff, int64_t ld_diff,
+    const int32_t* __restrict__ band_lo, const int32_t* __restrict__ band_hi, int32_t n_bands, int64_t rows,
+    int64_t seg_rows, const int64_t* __restrict__ seg, int32_t n_seg, int64_t run, float* __restrict__ odf) {
+  extern __shared__ float s_dyn[];                        // [warps][128 NV] maxima, band tables
+  constexpr int n_bins = 128 * NV;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  int* s_lo = reinterpret_cast<int*>(s_dyn + (size_t)warps * n_bins);
+  int* s_len = s_lo + n_bands;
+  for (int b = threadIdx.x; b < n_bands; b += blockDim.x) {
+    const int lo = band_lo[b], hi = band_hi[b];
+    s_lo[b] = lo; s_len[b] = hi > lo ? hi - lo : 0;
+  }
+  __syncthreads();
+  float* mx = s_dyn + (size_t)warp * n_bins;
+  const int64_t first = ((int64_t)blockIdx.x * warps + warp) * run;
+  if (first >= rows) return;
+  const int64_t stop = first + run < rows ? first + run : rows;
+
+  // [sig_lo, sig_hi): rows of the signal the current row belongs to
+  int64_t sig_lo = 0, sig_hi = rows;
+  int si = 0;
+  if (seg) {
+    si = find_segment(seg, n_seg, first);
+    sig_lo = seg[si]; sig_hi = seg[si + 1];
+  } else if (seg_rows > 0) {
+    sig_lo = (first / seg_rows) * seg_rows; sig_hi = sig_lo + seg_rows;
+  }
+  float4 P[NV], A[NV], B[NV];
+  cf_load_row<NV>(A, lgd + first * ld_lgd, lane);
+  if (first > sig_lo) cf_load_row<NV>(P, lgd + (first - 1) * ld_lgd, lane);
+  else {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) P[j] = A[j];
+  }
+  if (first + 1 < rows) cf_load_row<NV>(B, lgd + (first + 1) * ld_lgd, lane);
+
+  for (int64_t row = first; row < stop; ++row) {
+    if (row >= sig_hi) {                                  // first row of the next signal
+      if (seg) {
+        do { ++si; } while (seg[si + 1] <= row);          // empty signals have no rows
+        sig_lo = seg[si]; sig_hi = seg[si + 1];
+      } else {
+        sig_lo = sig_hi; sig_hi = sig_lo + seg_rows;
+      }
+    }
+    const bool last = row + 1 >= sig_hi;                  // 'reflect': the row itself stands in for its neighbour
+    float4* m4 = reinterpret_cast<float4*>(mx);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float4 m = fmax4(P[j], A[j]);
+      if (!last) m = fmax4(m, B[j]);
+      m4[lane + 32 * j] = m;
+    }
+    // shift the window and put the row after next in flight
+#pragma unroll
+    for (int j = 0; j < NV; ++j) { P[j] = last ? B[j] : A[j]; A[j] = B[j]; }
+    if (row + 2 < rows && row + 1 < stop) cf_load_row<NV>(B, lgd + (row + 2) * ld_lgd, lane);
+    __syncwarp();
+    float sum = 0.0f;
+    const float* drow = diff + row * ld_diff;
+    for (int b0 = 0; b0 < n_bands; b0 += 32) {
+      const int b = b0 + lane;
+      const bool have = b < n_bands;
+      const int lo = have ? s_lo[b] : 0, len = have ? s_len[b] : 0;
+      const float d = have ? drow[b] : 0.0f;
+      const int glen = __reduce_max_sync(0xffffffffu, len);
+      float m = INFINITY;
+      const int top = lo + (len > 0 ? len - 1 : 0);
+      for (int k = 0; k < glen; ++k) m = fminf(m, mx[min(lo + k, top)]);
+      sum = __fmaf_rn(d, len > 0 ? m : 0.0f, sum);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) odf[row] = sum;
+    __syncwarp();                                         // the maxima are overwritten by the next row
   }
 }
 
@@ -473,14 +570,32 @@ extern "C" MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, co
     return MMB_E_INVALID;
   if (rows == 0) return MMB_OK;
   const int warps = 8;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  // rows read once (streaming kernel) when the rows can be held as float4 registers
+  const bool vec_ok = temporal_filter == 3 && (n_bins == 512 || n_bins == 1024) && ld_lgd % 4 == 0 &&
+                      (reinterpret_cast<uintptr_t>(lgd_dev) & 15) == 0 && getenv("MMB_CF_GENERIC") == nullptr;
+  if (vec_ok) {
+    const size_t smem = ((size_t)warps * n_bins + 2 * (size_t)n_bands) * sizeof(float);
+    auto kern = n_bins == 1024 ? complex_flux_stream_kernel<8> : complex_flux_stream_kernel<4>;
+    if (smem > 48 * 1024 &&
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+      return MMB_E_CUDA;
+    const int64_t total_warps = (int64_t)sms * 2 * warps;          // two CTAs per SM
+    const int64_t run = (rows + total_warps - 1) / total_warps;
+    const int64_t used = (rows + run - 1) / run;
+    const unsigned grid = (unsigned)((used + warps - 1) / warps);
+    kern<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(lgd_dev, ld_lgd, diff_dev, ld_diff, band_lo_dev,
+                                                           band_hi_dev, n_bands, rows, rows_per_signal,
+                                                           seg_offsets_dev, n_segments, run, odf_dev);
+    return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+  }
   const size_t smem = ((size_t)warps * n_bins + (size_t)warps * n_bands + 3 * (size_t)n_bands + 1 + kCfMaxPieces) *
                       sizeof(float);
   if (smem > 48 * 1024 &&
       cudaFuncSetAttribute(complex_flux_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
     return MMB_E_CUDA;
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   int64_t grid = (rows + warps - 1) / warps;
   if (grid > (int64_t)sms * 4) grid = (int64_t)sms * 4;       // persistent CTAs, a multiple of the SM count
   complex_flux_kernel<<<(unsigned)grid, warps * 32, smem, (cudaStream_t)stream>>>(

@@ -418,3 +418,50 @@ def test_pcm_ingest_remix():
     assert a.shape == b.shape and np.array_equal(a, b)
     # a second call reuses the plan's pipeline buffers
     assert np.array_equal(fe.run_host(stereo, lens, ("diff",), num_channels=2)["diff"].numpy(), b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_bins", [1024, 512, 640])
+def test_complex_flux_kernel_ragged_signals(n_bins, monkeypatch):
+    """mmb_complex_flux on random matrices with signals of 1, 2, 3 and many rows back to back (temporal 'reflect'
+    maximum inside each signal, madmom/features/onsets.py:282-317): the streaming kernel (rows read once) and the
+    generic kernel give the same bits, and both match scipy's maximum_filter + the per-band minimum."""
+    torch = pytest.importorskip("torch")
+    from scipy.ndimage import maximum_filter
+    from madmom_b200 import _lib
+    rng = np.random.default_rng(n_bins)
+    lens = [1, 2, 3, 1, 57, 700, 2, 333, 1]
+    rows, B = sum(lens), 77
+    lgd = rng.random((rows, n_bins), dtype=np.float32)
+    diff = rng.random((rows, B), dtype=np.float32)
+    centres = np.unique(np.round(np.geomspace(2, n_bins - 3, B + 2)).astype(np.int64))
+    lo = np.zeros(B, np.int32); hi = np.zeros(B, np.int32)
+    for b in range(B):
+        c0 = centres[min(b, len(centres) - 3)]; c2 = centres[min(b, len(centres) - 3) + 2]
+        lo[b], hi[b] = max(c0 - 1, 0), min(c2 + 2, n_bins)
+    hi[5] = lo[5]                                                    # an empty band contributes nothing
+    seg = np.concatenate(([0], np.cumsum(lens))).astype(np.int64)
+    want = np.zeros(rows, np.float64)
+    for s in range(len(lens)):
+        a, e = seg[s], seg[s + 1]
+        mx = maximum_filter(lgd[a:e], size=[3, 1], origin=0)
+        mask = np.stack([mx[:, lo[b]:hi[b]].min(axis=1) if hi[b] > lo[b] else np.zeros(e - a, np.float32)
+                         for b in range(B)], axis=1)
+        want[a:e] = (diff[a:e].astype(np.float64) * mask).sum(axis=1)
+    dev = torch.device("cuda:0")
+    t = lambda x: torch.from_numpy(x).to(dev)
+    args = (t(lgd), t(diff), t(lo), t(hi))
+    got = _lib.complex_flux(*args, seg_offsets=t(seg)).cpu().numpy()
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-5)
+    monkeypatch.setenv("MMB_CF_GENERIC", "1")
+    generic = _lib.complex_flux(*args, seg_offsets=t(seg)).cpu().numpy()
+    assert np.array_equal(got, generic)
+    monkeypatch.delenv("MMB_CF_GENERIC")
+    # equal-length signals by rows_per_signal, and one signal only
+    lgd2, diff2 = t(lgd[:1000]), t(diff[:1000])
+    for rps in (0, 8, 250):
+        a = _lib.complex_flux(lgd2, diff2, args[2], args[3], rows_per_signal=rps).cpu().numpy()
+        monkeypatch.setenv("MMB_CF_GENERIC", "1")
+        b_ = _lib.complex_flux(lgd2, diff2, args[2], args[3], rows_per_signal=rps).cpu().numpy()
+        monkeypatch.delenv("MMB_CF_GENERIC")
+        assert np.array_equal(a, b_), rps

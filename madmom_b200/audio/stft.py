@@ -11,7 +11,7 @@ never materialises the (T, K) complex matrix at all.
 import numpy as np
 
 from ..processors import Processor
-from ..recipe import fft_frequencies  # noqa: F401  (re-exported, same name as the reference)
+from ..recipe import fft_frequencies, window_of  # noqa: F401  (fft_frequencies re-exported, same name as the reference)
 from .._engine import Chain
 from .signal import FramedSignal
 
@@ -130,8 +130,7 @@ class ShortTimeFourierTransform(DeviceResult):
             raise NotImplementedError("include_nyquist is not available on the GPU path")
         if frame_size not in (1024, 2048, 4096):
             raise NotImplementedError("frame_size must be 1024, 2048 or 4096 on the GPU path, not %d" % frame_size)
-        if callable(window):
-            window = window(frame_size)
+        window = window_of(window, frame_size)
         chain = Chain(frames, window=window, circular_shift=circular_shift, fft_window=fft_window)
         DeviceResult.__init__(self, chain)
         self.frames = frames

@@ -74,7 +74,8 @@ struct mmb_plan {
   int group_warps = 0;
   mmb::SmemLayout L;
   int ring_rows = 0;
-  int chunk_frames = 0;
+  int chunk_frames = 0;          // output frames per chunk of a launch with plenty of work (upper bound)
+  bool chunk_fixed = false;      // set by the caller / MMB_CHUNK_ROUNDS: never adapted to the size of a launch
   int n_passes = 0, max_q = 0, b_pad = 0, w_floats = 0, fb_iters = 0;
   float* d_win = nullptr;
   float2 *d_tw1 = nullptr, *d_tw2k = nullptr, *d_tw4k = nullptr;
@@ -88,6 +89,7 @@ struct mmb_layout {
   int32_t* d_prefix = nullptr;
   int32_t n = 0;
   int32_t total_chunks = 0;
+  int32_t chunk_frames = 0;   // output frames per chunk of this layout (pick_chunk_frames)
   int64_t total_rows = 0;
   int64_t pcm_extent = 0;     // max over units of pcm_offset + pcm_len
 };
@@ -325,8 +327,12 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)"); }
   const int fpr = mmb::frames_per_round(N, p->group_warps);
   int rounds = 32;
-  if (const char* env = std::getenv("MMB_CHUNK_ROUNDS")) rounds = std::max(std::atoi(env), 1);
+  if (const char* env = std::getenv("MMB_CHUNK_ROUNDS")) { rounds = std::max(std::atoi(env), 1); p->chunk_fixed = true; }
+  if (cfg->chunk_frames > 0) p->chunk_fixed = true;
   p->chunk_frames = cfg->chunk_frames > 0 ? cfg->chunk_frames : std::max(rounds * fpr - cfg->diff_frames, 1);
+  // N = 1024: even chunks, so that chunks of a unit with an even first frame start at even frames (the kernel pairs
+  // frames 2m, 2m + 1 and a chunk that starts at an odd frame computes one more lead-in frame)
+  if (N == 1024) p->chunk_frames = std::max(cfg->chunk_frames > 0 ? (p->chunk_frames + 1) & ~1 : p->chunk_frames & ~1, 2);
   *out = p;
   return MMB_OK;
 }
@@ -350,12 +356,30 @@ static int validate_units(const mmb_track* u, int32_t n) {
   return MMB_OK;
 }
 
-static void build_prefix(const mmb_plan* p, const mmb_track* u, int32_t n, std::vector<int32_t>& prefix,
-                         int64_t* rows) {
+// Output frames per chunk of one launch.  With plenty of work it is the plan's chunk (32 rounds: the lead-in frames
+// a chunk recomputes stay below 1 %).  A launch with fewer frames than that spreads over the SMs (one short file, the
+// drop-in use) gets the fewest rounds per chunk that still give every warp group at most one chunk, so the
+// latency is that of a few rounds instead of that of a whole chunk on one or two SMs.  Results do not depend on it.
+static int pick_chunk_frames(const mmb_plan* p, const mmb_track* u, int32_t n) {
+  if (p->chunk_fixed) return p->chunk_frames;
+  int64_t total = 0;
+  for (int32_t i = 0; i < n; ++i) total += u[i].frame_count;
+  const int fpr = mmb::frames_per_round(p->cfg.frame_size, p->group_warps);
+  const int64_t slots = (int64_t)p->num_sms * (p->warps / p->group_warps);
+  const int64_t per_slot = (total + slots - 1) / slots;
+  const int64_t rounds = std::max<int64_t>((per_slot + p->cfg.diff_frames + fpr - 1) / fpr, 1);
+  int64_t chunk = std::max<int64_t>(rounds * fpr - p->cfg.diff_frames, 1);
+  if (p->cfg.frame_size == 1024) chunk = std::max<int64_t>(chunk & ~(int64_t)1, 2);      // even, see mmb_plan_create
+  return (int)std::min<int64_t>(chunk, p->chunk_frames);
+}
+
+static void build_prefix(const mmb_plan* p, const mmb_track* u, int32_t n, int chunk_frames,
+                         std::vector<int32_t>& prefix, int64_t* rows) {
+  (void)p;
   prefix.assign(n + 1, 0);
   int64_t r = 0;
   for (int32_t i = 0; i < n; ++i) {
-    const int64_t c = (u[i].frame_count + p->chunk_frames - 1) / p->chunk_frames;
+    const int64_t c = (u[i].frame_count + chunk_frames - 1) / chunk_frames;
     prefix[i + 1] = prefix[i] + (int32_t)c;
     r += u[i].frame_count;
   }
@@ -378,7 +402,8 @@ extern "C" int mmb_layout_create(const mmb_plan* p, const mmb_track* units, int3
   mmb_layout* l = new (std::nothrow) mmb_layout();
   if (!l) return fail(MMB_E_NOMEM, "out of host memory");
   std::vector<int32_t> prefix;
-  build_prefix(p, units, n, prefix, &l->total_rows);
+  l->chunk_frames = pick_chunk_frames(p, units, n);
+  build_prefix(p, units, n, l->chunk_frames, prefix, &l->total_rows);
   l->n = n;
   l->total_chunks = prefix[n];
   for (int32_t i = 0; i < n; ++i) l->pcm_extent = std::max(l->pcm_extent, units[i].pcm_offset + units[i].pcm_len);
@@ -408,11 +433,11 @@ static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
 }
 
 static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_prefix, int32_t n, int32_t chunks,
-                  const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream) {
+                  int chunk_frames, const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream) {
   FrontendParams fp;
   std::memset(&fp, 0, sizeof(fp));
   fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunk_prefix = d_prefix; fp.n_tracks = n; fp.total_chunks = chunks;
-  fp.chunk_frames = p->chunk_frames; fp.hop = p->cfg.hop_size; fp.origin = p->cfg.origin; fp.span_cap = p->span_cap;
+  fp.chunk_frames = chunk_frames; fp.hop = p->cfg.hop_size; fp.origin = p->cfg.origin; fp.span_cap = p->span_cap;
   fp.win = p->d_win; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
   const bool band_out = o->filt || o->log || o->diff || o->odf;
   fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only stft/spec are wanted
@@ -444,7 +469,7 @@ extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_d
   int rc = check_outputs(p, outs);
   if (rc) return rc;
   CU(cudaSetDevice(p->cfg.device));
-  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, pcm_dev, l->pcm_extent, outs, (cudaStream_t)stream);
+  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, outs, (cudaStream_t)stream);
   if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
   return rc;
 }
@@ -537,7 +562,8 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
         tab[i - i0].out_row -= row0;
       }
       int64_t dummy;
-      build_prefix(p, reinterpret_cast<const mmb_track*>(tab.data()), i1 - i0, prefix, &dummy);
+      const int chunk_frames = pick_chunk_frames(p, reinterpret_cast<const mmb_track*>(tab.data()), i1 - i0);
+      build_prefix(p, reinterpret_cast<const mmb_track*>(tab.data()), i1 - i0, chunk_frames, prefix, &dummy);
       size_t pcm_bytes = (size_t)(pcm1 - pcm0) * sb;
       if (pcm_bytes == 0) pcm_bytes = sb;
       CUS(ensure(&S.d_pcm, &S.pcm_cap, pcm_bytes));
@@ -575,7 +601,7 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
       // pageable tab/prefix vectors are reused by the next group: the async copies above are staged
       // synchronously by the runtime for pageable memory, so this is safe.
       if (prefix.back() > 0) {
-        status = launch(p, S.d_tracks, S.d_prefix, (int32_t)tab.size(), prefix.back(), S.d_pcm, pcm1 - pcm0, &od,
+        status = launch(p, S.d_tracks, S.d_prefix, (int32_t)tab.size(), prefix.back(), chunk_frames, S.d_pcm, pcm1 - pcm0, &od,
                         S.stream);
         if (status) goto done;
         ++n_launch;

@@ -88,6 +88,9 @@ __device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, in
     d.pcm_offset = tr.pcm_offset; d.pcm_len = tr.pcm_len;
     d.sample_base = tr.sample_base;
     g0 = max(d.ga - (long long)lead, 0LL);
+    // N = 1024 packs frames (2m, 2m + 1) into one FFT: pairing by the global frame index (one more lead-in frame when
+    // needed; chunk sizes are even, capi.cu) keeps a frame's bits independent of how its unit is cut into chunks
+    if (N == 1024) g0 &= ~1LL;
   }
   d.g0 = g0;
   d.nfr = (int)min((long long)fpr, d.gb - g0);

@@ -65,12 +65,16 @@ def frame_shards(num_samples, hop_size, frame_size, world_size, origin=0, diff_f
     """[FrameShard] for every rank of `world_size`."""
     T = R.num_frames(num_samples, hop_size, end)
     per = -(-T // world_size) if T else 0
+    # frame_size 1024: the kernel packs frames (2m, 2m + 1) into one FFT, so ranges start at even frames and the
+    # halo reaches one frame further back; that keeps the shards bit-identical to the unsharded launch
+    pair = 1 if frame_size == 1024 else 0
+    per += per & pair
     shards = []
     for r in range(world_size):
         f0 = min(r * per, T)
         f1 = min(f0 + per, T)
         if f1 > f0:
-            lead = max(f0 - diff_frames, 0)
+            lead = max(f0 - diff_frames - pair, 0)
             s_lo = max(R.frame_start(lead, frame_size, hop_size, origin), 0)
             s_hi = min(R.frame_start(f1 - 1, frame_size, hop_size, origin) + frame_size, num_samples)
             s_hi = max(s_hi, s_lo)

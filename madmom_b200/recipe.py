@@ -37,12 +37,31 @@ def frame_start(index, frame_size, hop_size, origin=0):
     return int(index * hop_size) - int(frame_size) // 2 - int(origin)
 
 
+_NUMPY_WINDOWS = (np.hanning, np.hamming, np.blackman, np.bartlett)
+_window_cache = {}
+
+
+def window_of(window, frame_size):
+    """`window(frame_size)` for a callable window.  numpy's own window functions are pure, so their (read-only)
+    results are kept: a per-file call of the drop-in processors does not rebuild the window every time."""
+    if not callable(window):
+        return window
+    if not any(window is w for w in _NUMPY_WINDOWS):
+        return window(frame_size)
+    key = (window.__name__, int(frame_size))
+    w = _window_cache.get(key)
+    if w is None:
+        w = window(frame_size)
+        w.setflags(write=False)
+        _window_cache[key] = w
+    return w
+
+
 def fft_window(window, frame_size, signal_dtype):
     """float64 window actually multiplied onto the samples: integer PCM is left un-scaled and the window
     divided by iinfo(dtype).max instead (ShortTimeFourierTransform.__new__, madmom/audio/stft.py:331-349).
     window=None on float PCM means a rectangular window (the kernel always multiplies)."""
-    if callable(window):
-        window = window(frame_size)
+    window = window_of(window, frame_size)
     if window is not None:
         window = np.asarray(window, dtype=np.float64)
         if window.shape != (frame_size,):
@@ -61,9 +80,9 @@ def fft_frequencies(num_fft_bins, sample_rate):
 def diff_frames(diff_ratio, hop_size, frame_size, window=np.hanning):
     """_diff_frames, madmom/audio/spectrogram.py:834-864: first window sample above ratio * max, distance
     to the window centre in hops, Python (banker's) round, at least 1."""
-    if callable(window):
-        window = window(frame_size)
-    sample = np.argmax(window > float(diff_ratio) * max(window))
+    window = window_of(window, frame_size)
+    # the reference takes Python's max() of the array; np.max returns the same float64 without the per-element loop
+    sample = np.argmax(window > float(diff_ratio) * np.max(window))
     diff_samples = len(window) / 2 - sample
     return int(max(1, round(diff_samples / hop_size)))
 

@@ -129,6 +129,27 @@ def test_ragged_batch_vs_oracle(N, bpo, norm, mul, ratio):
         r0 += t
 
 
+@pytest.mark.parametrize("N,ratio", [(1024, 0.25), (1024, 0.5), (2048, 0.5), (4096, 0.25)])
+def test_rows_do_not_depend_on_chunking(N, ratio):
+    """A track's rows are bit-identical whatever the chunk size (the library's default, its choice for a small
+    launch, explicit odd / even sizes) and whether the track runs alone or inside a batch.  N = 1024 packs two
+    frames into one FFT: pairs are formed on the global frame index, not on the position inside a chunk."""
+    from madmom_b200.synth import make_track
+    lens = [50000, 44100 * 4 + 17, 441 * 37, 12345]
+    tracks = [make_track(2000 + i, num_samples=n) for i, n in enumerate(lens)]
+    ref = None
+    for chunk in (0, 13, 14, 50, 333):
+        plan, _ = _plan_for(np.int16, N, 441., 6, True, ratio=ratio, chunk_frames=chunk)
+        got, T = _run_all(plan, tracks, 441.)
+        if ref is None:
+            ref = got
+            alone, _ = _run_all(plan, tracks[1:2], 441.)       # a small launch: fewer rounds per chunk
+            for k in ("log", "diff", "odf", "spec"):
+                assert np.array_equal(alone[k], got[k][T[0]:T[0] + T[1]], equal_nan=True), (N, k)
+        for k in ("log", "diff", "odf", "spec", "stft"):
+            assert np.array_equal(got[k], ref[k], equal_nan=True), (N, chunk, k)
+
+
 def test_float32_pcm(ref_synth):
     from oracle import frontend as O
     from madmom_b200.synth import make_track

@@ -256,7 +256,7 @@ def test_long_signal_shards_on_one_gpu():
     from madmom_b200.batch import BatchFrontEnd
     from madmom_b200.synth import make_track
     x = make_track(11, num_samples=400003)
-    for rec in (R.SUPERFLUX, R.SUPERFLUX_200):
+    for rec in (R.SUPERFLUX, R.SUPERFLUX_200) + tuple(R.RNN_ONSET):       # RNN_ONSET: N = 1024 / 2048 / 4096
         whole = BatchFrontEnd(rec).run_device(torch.from_numpy(x).cuda(), [len(x)], ("diff", "odf"))
         T = whole["diff"].shape[0]
         fe = parallel.LongSignalFrontEnd(rec)

@@ -1,6 +1,7 @@
 """Glue between the lazy result objects (audio/stft.py, audio/spectrogram.py) and the CUDA library: turns the
 description of a chain (frames -> window/FFT -> filterbank -> log -> difference) into one cached `FrontEndPlan`
 and one fused kernel launch.  Nothing here computes on the host."""
+import hashlib
 import threading
 
 import numpy as np
@@ -27,6 +28,27 @@ def log_mode_of(log, mul, add):
             return mode
     raise NotImplementedError("log function %r is not available on the GPU path (np.log10, np.log, np.log2 or "
                               "None)" % (log,))
+
+
+def _filterbank_key(fb):
+    """Plan-cache key of a filterbank: shape + digest of its float32 bytes.  The digest is kept on the array (the
+    processors hand the same Filterbank object to every call, like the reference's cache in
+    FilteredSpectrogramProcessor) and the array is frozen from then on, so a later in-place change raises instead
+    of silently running with the plan of the old weights."""
+    if fb is None:
+        return None
+    key = getattr(fb, "_mmb_plan_key", None)
+    if key is not None and not fb.flags.writeable:
+        return key
+    arr = np.ascontiguousarray(fb, dtype=np.float32)
+    key = (arr.shape, hashlib.blake2b(arr.tobytes(), digest_size=16).digest())
+    if isinstance(fb, np.ndarray):
+        try:
+            fb._mmb_plan_key = key
+            fb.setflags(write=False)
+        except (AttributeError, ValueError):
+            pass
+    return key
 
 
 class Chain(object):
@@ -57,7 +79,7 @@ class Chain(object):
         fw = np.ascontiguousarray(self.resolved_fft_window(), dtype=np.float64)
         fb = self.filterbank
         key = (device, fr.frame_size, fr.hop_size, dtype.str, self.circular_shift, fw.tobytes(),
-               None if fb is None else (fb.shape, np.asarray(fb).tobytes()), self.log_mode, float(self.mul),
+               _filterbank_key(fb), self.log_mode, float(self.mul),
                float(self.add), self.diff_frames, self.diff_max_bins, self.positive_diffs)
         with _lock:
             plan = _plans.get(key)

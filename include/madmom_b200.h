@@ -126,6 +126,16 @@ MMB_API int mmb_layout_destroy(mmb_layout* layout);
 MMB_API int mmb_run(const mmb_plan* plan, const mmb_layout* layout, const void* pcm_dev, const mmb_outputs* outs,
             void* stream, int32_t* launches);
 
+/* Device path fused with the all-gather of a sharded long signal (the reference has no counterpart, it
+ * replaces mmb_run followed by ncclAllGather): dsts[0] are this GPU's matrices, dsts[1 .. n_dst-1] the SAME matrices
+ * of the other ranks mapped into this process (torch symmetric memory, cudaIpcOpenMemHandle, or cudaMalloc memory
+ * with peer access enabled), every pointer already offset to this rank's row range.  The kernel stores each row of
+ * log / diff / odf to all n_dst destinations as it is produced, so the NVLink transfer overlaps the computation
+ * row by row; the caller synchronises the ranks afterwards (barrier) before reading.  Only the band outputs log,
+ * diff and odf are allowed; all destinations must use the same leading dimensions.  n_dst <= 8. */
+MMB_API int mmb_run_gather(const mmb_plan* plan, const mmb_layout* layout, const void* pcm_dev,
+                           const mmb_outputs* dsts, int32_t n_dst, void* stream, int32_t* launches);
+
 /* Host path (what a madmom call site holding numpy arrays uses): pcm_host and the outputs are HOST
  * pointers (pinned for full speed); the library stages units through its own device buffers with
  * host-to-device copy, kernel and device-to-host copy overlapped on three streams, and returns when the

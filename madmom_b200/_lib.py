@@ -56,6 +56,7 @@ EXPORTS = {
     "mmb_layout_create": (c_i32, [c_vp, c_vp, c_i32, ctypes.POINTER(c_vp)]),
     "mmb_layout_destroy": (c_i32, [c_vp]),
     "mmb_run": (c_i32, [c_vp, c_vp, c_vp, ctypes.POINTER(Outputs), c_vp, ctypes.POINTER(c_i32)]),
+    "mmb_run_gather": (c_i32, [c_vp, c_vp, c_vp, ctypes.POINTER(Outputs), c_i32, c_vp, ctypes.POINTER(c_i32)]),
     "mmb_run_host": (c_i32, [c_vp, c_vp, c_i32, c_vp, ctypes.POINTER(Outputs), ctypes.POINTER(c_i32)]),
     "mmb_run_host_interleaved": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_i32, c_i32, ctypes.POINTER(Outputs),
                                          ctypes.POINTER(c_i32)]),
@@ -277,6 +278,32 @@ class FrontEndPlan(object):
         n = c_i32(0)
         _check(self._lib.mmb_run(self._handle, self._layout(units), pcm.data_ptr(), ctypes.byref(o), stream,
                                  ctypes.byref(n)))
+        launch_count += n.value
+        return n.value
+
+    def run_gather(self, pcm, units, destinations, stream=None):
+        """Device path fused with an all-gather (mmb_run_gather): `destinations` is a list of {name: (pointer,
+        leading dimension)} with name in log / diff / odf; entry 0 is this GPU's memory, the others are the peers'
+        buffers mapped into this process (torch symmetric memory), every pointer already offset to this rank's
+        rows.  Each row is stored to all destinations by the kernel.  Asynchronous on the current torch stream."""
+        global launch_count
+        import torch
+        units = np.ascontiguousarray(units, dtype=TRACK_DTYPE)
+        if not pcm.is_cuda or pcm.device.index != self.device or not pcm.is_contiguous():
+            raise ValueError("pcm must be a contiguous tensor on cuda:%d" % self.device)
+        arr = (Outputs * len(destinations))()
+        for i, dst in enumerate(destinations):
+            for name, (ptr, ld) in dst.items():
+                if name not in ("log", "diff", "odf"):
+                    raise ValueError("run_gather stores the outputs log, diff and odf only, not %r" % name)
+                setattr(arr[i], name, ptr)
+                if name != "odf":
+                    setattr(arr[i], "ld_" + name, ld)
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        n = c_i32(0)
+        _check(self._lib.mmb_run_gather(self._handle, self._layout(units), pcm.data_ptr(), arr, len(destinations),
+                                        stream, ctypes.byref(n)))
         launch_count += n.value
         return n.value
 

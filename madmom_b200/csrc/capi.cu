@@ -433,7 +433,8 @@ static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
 }
 
 static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_prefix, int32_t n, int32_t chunks,
-                  int chunk_frames, const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream) {
+                  int chunk_frames, const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream,
+                  const mmb_outputs* extra = nullptr, int n_extra = 0) {
   FrontendParams fp;
   std::memset(&fp, 0, sizeof(fp));
   fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunk_prefix = d_prefix; fp.n_tracks = n; fp.total_chunks = chunks;
@@ -453,6 +454,8 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
   fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;
   fp.out_lgd = o->lgd; fp.ld_lgd = o->ld_lgd;
+  fp.n_extra = n_extra;
+  for (int t = 0; t < n_extra; ++t) { fp.x_log[t] = extra[t].log; fp.x_diff[t] = extra[t].diff; fp.x_odf[t] = extra[t].odf; }
   const int groups = p->warps / p->group_warps;
   int grid = p->num_sms;                              // one persistent CTA per SM
   if (grid > (chunks + groups - 1) / groups) grid = (chunks + groups - 1) / groups;
@@ -470,6 +473,29 @@ extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_d
   if (rc) return rc;
   CU(cudaSetDevice(p->cfg.device));
   rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, outs, (cudaStream_t)stream);
+  if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
+  return rc;
+}
+
+extern "C" int mmb_run_gather(const mmb_plan* p, const mmb_layout* l, const void* pcm_dev, const mmb_outputs* dsts,
+                              int32_t n_dst, void* stream, int32_t* launches) {
+  if (launches) *launches = 0;
+  if (!p || !l || !pcm_dev || !dsts) return fail(MMB_E_INVALID, "null argument");
+  if (n_dst < 1 || n_dst > mmb::kMaxExtraDst + 1) return fail(MMB_E_INVALID, "n_dst must be in [1, 8]");
+  int rc = check_outputs(p, &dsts[0]);
+  if (rc) return rc;
+  if (dsts[0].stft || dsts[0].spec || dsts[0].filt || dsts[0].lgd)
+    return fail(MMB_E_UNSUPPORTED, "mmb_run_gather stores the band outputs log, diff and odf only");
+  for (int32_t t = 1; t < n_dst; ++t) {
+    const mmb_outputs& a = dsts[0];
+    const mmb_outputs& b = dsts[t];
+    if (b.stft || b.spec || b.filt || b.lgd || !a.log != !b.log || !a.diff != !b.diff || !a.odf != !b.odf ||
+        (a.log && a.ld_log != b.ld_log) || (a.diff && a.ld_diff != b.ld_diff))
+      return fail(MMB_E_INVALID, "every destination must hold the same outputs with the same leading dimensions");
+  }
+  CU(cudaSetDevice(p->cfg.device));
+  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, &dsts[0],
+              (cudaStream_t)stream, dsts + 1, n_dst - 1);
   if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
   return rc;
 }

@@ -214,10 +214,14 @@ __device__ __forceinline__ void warp_band_epilogue(const FrontendParams& p, int 
 // lagged difference of frame g against the ring row of frame g - d (phase C)
 __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lane, const float* cur,
                                                 const float* prev, bool has_prev, long long row) {
-  const int nb = p.n_bands;
+  const int nb = p.n_bands, nx = p.n_extra;
   if (p.out_log) {
     float* o = p.out_log + row * p.ld_log;
     for (int b = lane; b < nb; b += 32) o[b] = cur[b];
+    for (int t = 0; t < nx; ++t) {                       // fused all-gather: the same row into the peers' matrices
+      float* ox = p.x_log[t] + row * p.ld_log;
+      for (int b = lane; b < nb; b += 32) ox[b] = cur[b];
+    }
   }
   if (p.out_diff == nullptr && p.out_odf == nullptr) return;
   float sum = 0.0f;
@@ -241,13 +245,19 @@ __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lan
       dv = cur[b] - ref;
       if (p.positive) dv = fmaxf(dv, 0.0f);
     }
-    if (p.out_diff) p.out_diff[row * p.ld_diff + b] = dv;
+    if (p.out_diff) {
+      p.out_diff[row * p.ld_diff + b] = dv;
+      for (int t = 0; t < nx; ++t) p.x_diff[t][row * p.ld_diff + b] = dv;
+    }
     sum += dv;
   }
   if (p.out_odf) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane == 0) p.out_odf[row] = sum;
+    if (lane == 0) {
+      p.out_odf[row] = sum;
+      for (int t = 0; t < nx; ++t) p.x_odf[t][row] = sum;
+    }
   }
 }
 

@@ -35,6 +35,8 @@ struct SmemLayout {
   int pcm_stride;        // bytes of staged PCM span per warp group
 };
 
+constexpr int kMaxExtraDst = 7;      // destinations of one launch besides the local one (8 GPUs of a node)
+
 struct FrontendParams {
   const void* pcm;               // int16 or float32 samples
   int64_t pcm_extent;            // elements of the PCM buffer that may be read (max over units of offset + len)
@@ -77,6 +79,12 @@ struct FrontendParams {
   float* out_diff;  int64_t ld_diff;
   float* out_odf;
   float* out_lgd;   int64_t ld_lgd;   // |local group delay| / pi (ComplexFlux), N = 2048 only
+  // fused all-gather (mmb_run_gather): the rows of log / diff / odf are also stored to n_extra further destinations
+  // (peer memory of the other ranks over NVLink), same leading dimensions as the local matrices
+  int32_t n_extra;
+  float* x_log[kMaxExtraDst];
+  float* x_diff[kMaxExtraDst];
+  float* x_odf[kMaxExtraDst];
 };
 
 constexpr int kMaxWarps = 16;

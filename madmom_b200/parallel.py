@@ -127,6 +127,51 @@ class LongSignalFrontEnd(object):
             self.plan.run(pcm_slice, units, {n: t[:shard.frame_count] for n, t in out.items()})
         return out
 
+    def run_fused(self, pcm_slice, num_samples, outputs=("diff",), group=None):
+        """Like run(), but without a separate collective: the front-end kernel stores every output row straight
+        into the result matrices of ALL ranks (peer memory over NVLink, torch symmetric memory for the mapping;
+        mmb_run_gather), so the transfer overlaps the computation row by row and the step ends with one barrier.
+        Returns {name: (T, cols) tensor}: views of this rank's symmetric buffers, valid until the next call with
+        the same shapes.  Bit-identical to run()."""
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        group = dist.group.WORLD if group is None else group
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        shard = self.shard(num_samples, world, rank)
+        T = R.num_frames(num_samples, self.recipe.hop_size, self.recipe.end)
+        per = shard.rows_per_rank
+        dev = torch.device("cuda", self.device)
+        if not hasattr(self, "_symm"):
+            self._symm = {}
+        bufs, handles = {}, {}
+        for n in outputs:
+            if n not in ("log", "diff", "odf"):
+                raise ValueError("run_fused gathers the outputs log, diff and odf, not %r" % n)
+            cols = 1 if n == "odf" else self.plan.width(n)
+            key = (n, world, per, cols)
+            if key not in self._symm:
+                buf = symm.empty((world * max(per, 1), cols), dtype=torch.float32, device=dev)
+                buf.zero_()
+                self._symm[key] = (buf, symm.rendezvous(buf, group))
+            bufs[n], handles[n] = self._symm[key]
+        first = handles[outputs[0]]
+        first.barrier(channel=0)             # every rank is done with the results of the previous call
+        if shard.frame_count > 0:
+            units = np.zeros(1, dtype=_lib.TRACK_DTYPE)
+            units[0] = shard.unit()
+            dsts = []
+            for p in [rank] + [q for q in range(world) if q != rank]:
+                d = {}
+                for n in outputs:
+                    cols = bufs[n].shape[1]
+                    d[n] = (int(handles[n].buffer_ptrs[p]) + rank * per * cols * 4, cols)
+                dsts.append(d)
+            self.plan.run_gather(pcm_slice, units, dsts)
+        first.barrier(channel=0)             # all peers have finished storing into this rank's buffers
+        return {n: (bufs[n][:T, 0] if n == "odf" else bufs[n][:T]) for n in outputs}
+
     def run(self, pcm_slice, num_samples, outputs=("diff",), group=None):
         """Compute this rank's slice and all-gather: every rank returns the full (T, cols) matrices."""
         import torch.distributed as dist

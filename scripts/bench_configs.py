@@ -111,6 +111,22 @@ def main():
                    "rows_per_rank": sh.rows_per_rank, "halo_samples": [1024 + fe.plan.diff_frames * 441, 1024],
                    "collective": "one all_gather_into_tensor of (rows_per_rank, 140) f32 per rank" if world > 1
                    else "none (single rank)"}
+            if world > 1:
+                # the same step with the all-gather fused into the kernel (rows stored straight into every rank's
+                # result over NVLink, mmb_run_gather), checked against the NCCL result, then timed
+                want = step()
+                got = fe.run_fused(sl, n, ("diff",))["diff"]
+                torch.cuda.synchronize()
+                same = bool(torch.equal(got, want))
+                del want, got
+                ms_f = reduce_max(timed(lambda: fe.run_fused(sl, n, ("diff",)), args.steps, args.warmup, torch, barrier))
+                if rank == 0:
+                    c2 = dict(cfg, collective="none: kernel stores each row to all ranks' symmetric-memory buffers "
+                              "(mmb_run_gather) + one barrier", bit_identical_to_nccl_path=same)
+                    print(json.dumps({"metric": "audio-seconds per second (x realtime)",
+                                      "value": frames / fps / (ms_f * 1e-3), "unit": "audio-s/s", "n_gpus": world,
+                                      "ms_per_step": ms_f, "steps": args.steps, "frames_per_step": frames,
+                                      "config": c2}), flush=True)
             del sl
         else:
             raise SystemExit("unknown config %r" % name)

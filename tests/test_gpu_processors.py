@@ -273,6 +273,38 @@ def test_long_signal_shards_on_one_gpu():
                 assert torch.equal(full, whole[k]), (rec.hop_size, world, k)
 
 
+def test_run_gather_stores_every_row_to_all_destinations():
+    """mmb_run_gather (the front end fused with the all-gather of a sharded long signal): with three destinations
+    on this GPU standing in for the ranks' buffers, every destination receives the rows mmb_run produces, bit for
+    bit, for each shard of a 4-rank split; misuse is rejected."""
+    from madmom_b200 import _lib, parallel, recipe as R
+    from madmom_b200.synth import make_track
+    x = make_track(12, num_samples=300001)
+    for rec in (R.SUPERFLUX_200, R.RNN_ONSET[0]):
+        fe = parallel.LongSignalFrontEnd(rec)
+        B = fe.plan.num_bands
+        for rank in range(4):
+            sh = fe.shard(len(x), 4, rank)
+            pcm = torch.from_numpy(x[sh.sample_lo:sh.sample_hi].copy()).cuda()
+            want = fe.run_local(pcm, sh, ("log", "diff", "odf"))
+            rows = sh.rows_per_rank
+            dst = [{"log": torch.zeros((rows, B), device="cuda"), "diff": torch.zeros((rows, B), device="cuda"),
+                    "odf": torch.zeros((rows,), device="cuda")} for _ in range(3)]
+            units = np.zeros(1, dtype=_lib.TRACK_DTYPE)
+            units[0] = sh.unit()
+            n = fe.plan.run_gather(pcm, units, [{k: (t.data_ptr(), t.stride(0) if t.dim() == 2 else 1)
+                                                 for k, t in d.items()} for d in dst])
+            assert n == 1
+            for d in dst:
+                for k in ("log", "diff", "odf"):
+                    assert torch.equal(d[k], want[k]), (rec.frame_size, rank, k)
+    with pytest.raises(ValueError):
+        fe.plan.run_gather(pcm, units, [{"spec": (dst[0]["log"].data_ptr(), B)}])
+    with pytest.raises((ValueError, _lib.LibraryError)):          # destinations must agree on the leading dimension
+        fe.plan.run_gather(pcm, units, [{"diff": (dst[0]["diff"].data_ptr(), B)},
+                                        {"diff": (dst[1]["diff"].data_ptr(), B + 1)}])
+
+
 def test_batch_front_end_stack_and_host_path():
     from oracle import frontend as O
     from madmom_b200 import recipe as R

@@ -131,8 +131,8 @@ class LongSignalFrontEnd(object):
         """Like run(), but without a separate collective: the front-end kernel stores every output row straight
         into the result matrices of ALL ranks (peer memory over NVLink, torch symmetric memory for the mapping;
         mmb_run_gather), so the transfer overlaps the computation row by row and the step ends with one barrier.
-        Returns {name: (T, cols) tensor}: views of this rank's symmetric buffers, valid until the next call with
-        the same shapes.  Bit-identical to run()."""
+        Returns {name: (T, cols) tensor}: views of this rank's symmetric buffers (row stride padded to a multiple
+        of 32 floats), valid until the next call with the same shapes.  Bit-identical to run()."""
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
@@ -149,7 +149,9 @@ class LongSignalFrontEnd(object):
         for n in outputs:
             if n not in ("log", "diff", "odf"):
                 raise ValueError("run_fused gathers the outputs log, diff and odf, not %r" % n)
-            cols = 1 if n == "odf" else self.plan.width(n)
+            # rows padded to whole 128-byte lines: every row then starts on a line, and the kernel's remote stores
+            # are full NVLink write packets instead of two partial ones each (the padding is never written)
+            cols = 1 if n == "odf" else -(-self.plan.width(n) // 32) * 32
             key = (n, world, per, cols)
             if key not in self._symm:
                 buf = symm.empty((world * max(per, 1), cols), dtype=torch.float32, device=dev)
@@ -170,7 +172,7 @@ class LongSignalFrontEnd(object):
                 dsts.append(d)
             self.plan.run_gather(pcm_slice, units, dsts)
         first.barrier(channel=0)             # all peers have finished storing into this rank's buffers
-        return {n: (bufs[n][:T, 0] if n == "odf" else bufs[n][:T]) for n in outputs}
+        return {n: (bufs[n][:T, 0] if n == "odf" else bufs[n][:T, :self.plan.width(n)]) for n in outputs}
 
     def run(self, pcm_slice, num_samples, outputs=("diff",), group=None):
         """Compute this rank's slice and all-gather: every rank returns the full (T, cols) matrices."""

@@ -136,6 +136,13 @@ MMB_API int mmb_run(const mmb_plan* plan, const mmb_layout* layout, const void* 
 MMB_API int mmb_run_gather(const mmb_plan* plan, const mmb_layout* layout, const void* pcm_dev,
                            const mmb_outputs* dsts, int32_t n_dst, void* stream, int32_t* launches);
 
+/* Same, through an NVLS multicast mapping (NVSwitch): the pointers of `mc` are MULTICAST addresses of the ranks'
+ * result matrices (torch symmetric memory: multicast_ptr; cuMulticastCreate / cuMulticastBindMem), offset to this
+ * rank's rows.  The kernel stores each row once with multimem.st and the switch delivers it to every GPU of the
+ * multicast object, this one included, so a row leaves the GPU once instead of once per peer. */
+MMB_API int mmb_run_multicast(const mmb_plan* plan, const mmb_layout* layout, const void* pcm_dev,
+                              const mmb_outputs* mc, void* stream, int32_t* launches);
+
 /* Host path (what a madmom call site holding numpy arrays uses): pcm_host and the outputs are HOST
  * pointers (pinned for full speed); the library stages units through its own device buffers with
  * host-to-device copy, kernel and device-to-host copy overlapped on three streams, and returns when the

@@ -57,6 +57,7 @@ EXPORTS = {
     "mmb_layout_destroy": (c_i32, [c_vp]),
     "mmb_run": (c_i32, [c_vp, c_vp, c_vp, ctypes.POINTER(Outputs), c_vp, ctypes.POINTER(c_i32)]),
     "mmb_run_gather": (c_i32, [c_vp, c_vp, c_vp, ctypes.POINTER(Outputs), c_i32, c_vp, ctypes.POINTER(c_i32)]),
+    "mmb_run_multicast": (c_i32, [c_vp, c_vp, c_vp, ctypes.POINTER(Outputs), c_vp, ctypes.POINTER(c_i32)]),
     "mmb_run_host": (c_i32, [c_vp, c_vp, c_i32, c_vp, ctypes.POINTER(Outputs), ctypes.POINTER(c_i32)]),
     "mmb_run_host_interleaved": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_i32, c_i32, ctypes.POINTER(Outputs),
                                          ctypes.POINTER(c_i32)]),
@@ -281,11 +282,13 @@ class FrontEndPlan(object):
         launch_count += n.value
         return n.value
 
-    def run_gather(self, pcm, units, destinations, stream=None):
+    def run_gather(self, pcm, units, destinations, stream=None, multicast=False):
         """Device path fused with an all-gather (mmb_run_gather): `destinations` is a list of {name: (pointer,
         leading dimension)} with name in log / diff / odf; entry 0 is this GPU's memory, the others are the peers'
         buffers mapped into this process (torch symmetric memory), every pointer already offset to this rank's
-        rows.  Each row is stored to all destinations by the kernel.  Asynchronous on the current torch stream."""
+        rows.  Each row is stored to all destinations by the kernel.  multicast=True: `destinations` is ONE entry
+        of NVLS multicast addresses (mmb_run_multicast: one multimem.st per value, the NVSwitch replicates it).
+        Asynchronous on the current torch stream."""
         global launch_count
         import torch
         units = np.ascontiguousarray(units, dtype=TRACK_DTYPE)
@@ -302,8 +305,14 @@ class FrontEndPlan(object):
         if stream is None:
             stream = torch.cuda.current_stream(self.device).cuda_stream
         n = c_i32(0)
-        _check(self._lib.mmb_run_gather(self._handle, self._layout(units), pcm.data_ptr(), arr, len(destinations),
-                                        stream, ctypes.byref(n)))
+        if multicast:
+            if len(destinations) != 1:
+                raise ValueError("a multicast launch has one destination: the multicast addresses")
+            _check(self._lib.mmb_run_multicast(self._handle, self._layout(units), pcm.data_ptr(), arr, stream,
+                                               ctypes.byref(n)))
+        else:
+            _check(self._lib.mmb_run_gather(self._handle, self._layout(units), pcm.data_ptr(), arr,
+                                            len(destinations), stream, ctypes.byref(n)))
         launch_count += n.value
         return n.value
 

@@ -434,7 +434,7 @@ static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
 
 static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_prefix, int32_t n, int32_t chunks,
                   int chunk_frames, const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream,
-                  const mmb_outputs* extra = nullptr, int n_extra = 0) {
+                  const mmb_outputs* extra = nullptr, int n_extra = 0, bool multicast = false) {
   FrontendParams fp;
   std::memset(&fp, 0, sizeof(fp));
   fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunk_prefix = d_prefix; fp.n_tracks = n; fp.total_chunks = chunks;
@@ -454,7 +454,7 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
   fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;
   fp.out_lgd = o->lgd; fp.ld_lgd = o->ld_lgd;
-  fp.n_extra = n_extra;
+  fp.n_extra = n_extra; fp.multicast = multicast ? 1 : 0;
   for (int t = 0; t < n_extra; ++t) { fp.x_log[t] = extra[t].log; fp.x_diff[t] = extra[t].diff; fp.x_odf[t] = extra[t].odf; }
   const int groups = p->warps / p->group_warps;
   int grid = p->num_sms;                              // one persistent CTA per SM
@@ -496,6 +496,21 @@ extern "C" int mmb_run_gather(const mmb_plan* p, const mmb_layout* l, const void
   CU(cudaSetDevice(p->cfg.device));
   rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, &dsts[0],
               (cudaStream_t)stream, dsts + 1, n_dst - 1);
+  if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
+  return rc;
+}
+
+extern "C" int mmb_run_multicast(const mmb_plan* p, const mmb_layout* l, const void* pcm_dev, const mmb_outputs* mc,
+                                 void* stream, int32_t* launches) {
+  if (launches) *launches = 0;
+  if (!p || !l || !pcm_dev || !mc) return fail(MMB_E_INVALID, "null argument");
+  int rc = check_outputs(p, mc);
+  if (rc) return rc;
+  if (mc->stft || mc->spec || mc->filt || mc->lgd)
+    return fail(MMB_E_UNSUPPORTED, "mmb_run_multicast stores the band outputs log, diff and odf only");
+  CU(cudaSetDevice(p->cfg.device));
+  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, mc,
+              (cudaStream_t)stream, nullptr, 0, true);
   if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
   return rc;
 }

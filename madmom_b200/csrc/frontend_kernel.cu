@@ -211,13 +211,21 @@ __device__ __forceinline__ void warp_band_epilogue(const FrontendParams& p, int 
   }
 }
 
+// store through an NVLS multicast address: the NVSwitch delivers the value to the same offset of every GPU bound to
+// the multicast object (this one included), so a gathered row leaves the SM once instead of once per peer
+__device__ __forceinline__ void mc_store(float* a, float v) {
+  asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
+}
+
 // lagged difference of frame g against the ring row of frame g - d (phase C)
 __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lane, const float* cur,
                                                 const float* prev, bool has_prev, long long row) {
   const int nb = p.n_bands, nx = p.n_extra;
+  const bool mc = p.multicast != 0;
   if (p.out_log) {
     float* o = p.out_log + row * p.ld_log;
-    for (int b = lane; b < nb; b += 32) o[b] = cur[b];
+    if (mc) for (int b = lane; b < nb; b += 32) mc_store(o + b, cur[b]);
+    else for (int b = lane; b < nb; b += 32) o[b] = cur[b];
     for (int t = 0; t < nx; ++t) {                       // fused all-gather: the same row into the peers' matrices
       float* ox = p.x_log[t] + row * p.ld_log;
       for (int b = lane; b < nb; b += 32) ox[b] = cur[b];
@@ -246,7 +254,8 @@ __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lan
       if (p.positive) dv = fmaxf(dv, 0.0f);
     }
     if (p.out_diff) {
-      p.out_diff[row * p.ld_diff + b] = dv;
+      if (mc) mc_store(p.out_diff + row * p.ld_diff + b, dv);
+      else p.out_diff[row * p.ld_diff + b] = dv;
       for (int t = 0; t < nx; ++t) p.x_diff[t][row * p.ld_diff + b] = dv;
     }
     sum += dv;
@@ -255,7 +264,8 @@ __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lan
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     if (lane == 0) {
-      p.out_odf[row] = sum;
+      if (mc) mc_store(p.out_odf + row, sum);
+      else p.out_odf[row] = sum;
       for (int t = 0; t < nx; ++t) p.x_odf[t][row] = sum;
     }
   }

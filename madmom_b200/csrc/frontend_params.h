@@ -82,6 +82,7 @@ struct FrontendParams {
   // fused all-gather (mmb_run_gather): the rows of log / diff / odf are also stored to n_extra further destinations
   // (peer memory of the other ranks over NVLink), same leading dimensions as the local matrices
   int32_t n_extra;
+  int32_t multicast;             // out_log / out_diff / out_odf are NVLS multicast addresses: stored with multimem.st
   float* x_log[kMaxExtraDst];
   float* x_diff[kMaxExtraDst];
   float* x_odf[kMaxExtraDst];

@@ -15,6 +15,8 @@ Two cases:
 The shard arithmetic is pure Python (testable on CPU with the gloo backend); only `LongSignalFrontEnd.run`
 touches the GPU.
 """
+import os
+
 import numpy as np
 
 from . import recipe as R
@@ -127,12 +129,15 @@ class LongSignalFrontEnd(object):
             self.plan.run(pcm_slice, units, {n: t[:shard.frame_count] for n, t in out.items()})
         return out
 
-    def run_fused(self, pcm_slice, num_samples, outputs=("diff",), group=None):
+    def run_fused(self, pcm_slice, num_samples, outputs=("diff",), group=None, multicast=None):
         """Like run(), but without a separate collective: the front-end kernel stores every output row straight
         into the result matrices of ALL ranks (peer memory over NVLink, torch symmetric memory for the mapping;
         mmb_run_gather), so the transfer overlaps the computation row by row and the step ends with one barrier.
         Returns {name: (T, cols) tensor}: views of this rank's symmetric buffers (row stride padded to a multiple
-        of 32 floats), valid until the next call with the same shapes.  Bit-identical to run()."""
+        of 32 floats), valid until the next call with the same shapes.  Bit-identical to run().
+        multicast: store through the NVLS multicast mapping of the buffers (one multimem.st per value, replicated
+        by the NVSwitch) instead of one store per peer; None = when the symmetric memory has one (and
+        MMB_GATHER_MULTICAST is not "0")."""
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
@@ -163,14 +168,21 @@ class LongSignalFrontEnd(object):
         if shard.frame_count > 0:
             units = np.zeros(1, dtype=_lib.TRACK_DTYPE)
             units[0] = shard.unit()
+            mc_ptrs = {n: int(getattr(handles[n], "multicast_ptr", 0) or 0) for n in outputs}
+            if multicast is None:
+                multicast = all(mc_ptrs.values()) and os.environ.get("MMB_GATHER_MULTICAST", "1") != "0"
+            if multicast and not all(mc_ptrs.values()):
+                raise RuntimeError("the symmetric memory of this group has no multicast (NVLS) mapping")
             dsts = []
-            for p in [rank] + [q for q in range(world) if q != rank]:
+            if multicast:
+                dsts.append({n: (mc_ptrs[n] + rank * per * bufs[n].shape[1] * 4, bufs[n].shape[1]) for n in outputs})
+            for p in ([] if multicast else [rank] + [q for q in range(world) if q != rank]):
                 d = {}
                 for n in outputs:
                     cols = bufs[n].shape[1]
                     d[n] = (int(handles[n].buffer_ptrs[p]) + rank * per * cols * 4, cols)
                 dsts.append(d)
-            self.plan.run_gather(pcm_slice, units, dsts)
+            self.plan.run_gather(pcm_slice, units, dsts, multicast=bool(multicast))
         first.barrier(channel=0)             # all peers have finished storing into this rank's buffers
         return {n: (bufs[n][:T, 0] if n == "odf" else bufs[n][:T, :self.plan.width(n)]) for n in outputs}
 

@@ -114,19 +114,27 @@ def main():
             if world > 1:
                 # the same step with the all-gather fused into the kernel (rows stored straight into every rank's
                 # result over NVLink, mmb_run_gather), checked against the NCCL result, then timed
-                want = step()
-                got = fe.run_fused(sl, n, ("diff",))["diff"]
-                torch.cuda.synchronize()
-                same = bool(torch.equal(got, want))
-                del want, got
-                ms_f = reduce_max(timed(lambda: fe.run_fused(sl, n, ("diff",)), args.steps, args.warmup, torch, barrier))
-                if rank == 0:
-                    c2 = dict(cfg, collective="none: kernel stores each row to all ranks' symmetric-memory buffers "
-                              "(mmb_run_gather) + one barrier", bit_identical_to_nccl_path=same)
-                    print(json.dumps({"metric": "audio-seconds per second (x realtime)",
-                                      "value": frames / fps / (ms_f * 1e-3), "unit": "audio-s/s", "n_gpus": world,
-                                      "ms_per_step": ms_f, "steps": args.steps, "frames_per_step": frames,
-                                      "config": c2}), flush=True)
+                for mc, how in ((False, "none: kernel stores each row to all ranks' symmetric-memory buffers "
+                                 "(mmb_run_gather) + one barrier"),
+                                (True, "none: kernel stores each row once through the NVLS multicast mapping of the "
+                                 "ranks' symmetric-memory buffers (mmb_run_multicast) + one barrier")):
+                    try:
+                        got = fe.run_fused(sl, n, ("diff",), multicast=mc)["diff"]
+                    except RuntimeError as e:                     # no multicast mapping on this box
+                        if rank == 0:
+                            print(json.dumps({"config": dict(cfg, collective=how), "unavailable": str(e)}), flush=True)
+                        continue
+                    torch.cuda.synchronize()
+                    same = bool(torch.equal(got, step()))
+                    del got
+                    ms_f = reduce_max(timed(lambda: fe.run_fused(sl, n, ("diff",), multicast=mc), args.steps,
+                                            args.warmup, torch, barrier))
+                    if rank == 0:
+                        c2 = dict(cfg, collective=how, bit_identical_to_nccl_path=same)
+                        print(json.dumps({"metric": "audio-seconds per second (x realtime)",
+                                          "value": frames / fps / (ms_f * 1e-3), "unit": "audio-s/s", "n_gpus": world,
+                                          "ms_per_step": ms_f, "steps": args.steps, "frames_per_step": frames,
+                                          "config": c2}), flush=True)
             del sl
         else:
             raise SystemExit("unknown config %r" % name)

@@ -11,7 +11,8 @@ dist.init_process_group("nccl", device_id=dev)
 t = symm.empty((world, 1 << 20), dtype=torch.float32, device=dev)
 t.zero_()
 h = symm.rendezvous(t, dist.group.WORLD)
-print(rank, "ptrs", [hex(p) for p in h.buffer_ptrs], "rank", h.rank, "world", h.world_size, flush=True)
+print(rank, "ptrs", [hex(p) for p in h.buffer_ptrs], "rank", h.rank, "world", h.world_size, "multicast_ptr",
+      hex(getattr(h, "multicast_ptr", 0) or 0), flush=True)
 h.barrier(channel=0)
 for p in range(world):
     peer = h.get_buffer(p, (world, 1 << 20), torch.float32)

@@ -23,8 +23,8 @@ def main():
         sh = fe.shard(len(x), world, rank)
         pcm = torch.from_numpy(x[sh.sample_lo:sh.sample_hi].copy()).cuda()
         want = fe.run(pcm, len(x), ("log", "diff", "odf"))
-        for _ in range(3):                                     # the symmetric buffers are reused between calls
-            got = fe.run_fused(pcm, len(x), ("log", "diff", "odf"))
+        for mc in (False, None, False, None):                  # peer stores / NVLS multicast when the box has it;
+            got = fe.run_fused(pcm, len(x), ("log", "diff", "odf"), multicast=mc)   # the buffers are reused
             torch.cuda.synchronize()
             for k in ("log", "diff", "odf"):
                 assert got[k].shape == want[k].shape, (k, got[k].shape, want[k].shape)

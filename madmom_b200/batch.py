@@ -154,7 +154,7 @@ class BatchFrontEnd(object):
 def complex_flux_batch(fe, pcm, lengths, temporal_filter=3, scratch_bytes=None):
     """ComplexFlux ODF (config 5 of BASELINE.json) for a batch of tracks on the device.  The per-bin local group
     delay matrix is an intermediate of rows x K floats, so the batch is walked in groups of tracks whose scratch
-    fits `scratch_bytes` (default: 8 GiB or a quarter of the free device memory; large groups keep the tail of
+    fits `scratch_bytes` (default: 16 GiB or a quarter of the free device memory; large groups keep the tail of
     the persistent front-end kernel short); per group: one fused front-end launch (lgd + difference) and one
     mmb_complex_flux launch.
     `fe` is a BatchFrontEnd built from a single circular-shift recipe (recipe.COMPLEXFLUX)."""
@@ -164,7 +164,7 @@ def complex_flux_batch(fe, pcm, lengths, temporal_filter=3, scratch_bytes=None):
         raise ValueError("complex_flux_batch needs a single recipe")
     pcm = pcm.reshape(-1)
     if scratch_bytes is None:
-        scratch_bytes = min(8 << 30, torch.cuda.mem_get_info(pcm.device)[0] // 4)
+        scratch_bytes = min(16 << 30, torch.cuda.mem_get_info(pcm.device)[0] // 4)
     T = fe.frame_counts(lengths)
     offsets = np.concatenate(([0], np.cumsum(lengths)[:-1])).astype(np.int64)
     rows_total = int(sum(T))

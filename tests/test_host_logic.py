@@ -207,3 +207,36 @@ def test_product_does_not_import_the_oracle():
             "bad = [m for m in sys.modules if m == 'oracle' or m.startswith('oracle.') or m.startswith('scipy.fft')]; "
             "sys.exit(1 if bad else 0)")
     assert subprocess.call([sys.executable, "-c", code], cwd=ROOT) == 0
+
+
+def test_window_cache_and_plan_key():
+    """Per-file overheads of the drop-in path: numpy's window functions are built once per frame size (read-only),
+    other callables every time; the plan-cache key of a filterbank is a digest kept on the frozen array;
+    diff_frames keeps the reference's values (tests/test_audio_spectrogram.py:459-480 via ref_framing)."""
+    from madmom_b200 import recipe as R
+    from madmom_b200._engine import _filterbank_key
+    from madmom_b200.audio.filters import LogarithmicFilterbank
+    w = R.window_of(np.hanning, 2048)
+    assert w is R.window_of(np.hanning, 2048) and not w.flags.writeable
+    assert np.array_equal(w, np.hanning(2048))
+    calls = []
+
+    def custom(n):
+        calls.append(n)
+        return np.ones(n)
+    assert R.window_of(custom, 8).shape == (8,) and R.window_of(custom, 8) is not R.window_of(custom, 8)
+    assert calls == [8, 8, 8]
+    given = np.arange(4.)
+    assert R.window_of(given, 4) is given and R.window_of(None, 4) is None
+    for ratio, hop, N, want in ((0.5, 441., 2048, 1), (0.5, 220.5, 2048, 2), (0.25, 441., 4096, 3),
+                                (0.5, 220.5, 4096, 5), (0.25, 441., 1024, 1)):
+        assert R.diff_frames(ratio, hop, N) == want
+    fb = LogarithmicFilterbank(R.fft_frequencies(1024, 44100), num_bands=24, norm_filters=False)
+    k1 = _filterbank_key(fb)
+    assert k1 == _filterbank_key(fb) and not fb.flags.writeable and k1[0] == (1024, 140)
+    other = LogarithmicFilterbank(R.fft_frequencies(1024, 44100), num_bands=12, norm_filters=False)
+    assert _filterbank_key(other) != k1 and _filterbank_key(None) is None
+    with pytest.raises(ValueError):
+        fb[0, 0] = 1.0                      # frozen: a changed filterbank cannot run with the old plan
+    same = LogarithmicFilterbank(R.fft_frequencies(1024, 44100), num_bands=24, norm_filters=False)
+    assert _filterbank_key(same) == k1      # equal weights, another object: same plan

@@ -218,10 +218,13 @@ __device__ __forceinline__ void mc_store(float* a, float v) {
 }
 
 // lagged difference of frame g against the ring row of frame g - d (phase C)
+// GATHER: the launch also stores to peer / multicast destinations (mmb_run_gather, mmb_run_multicast); the plain
+// launches are a separate instantiation without that code (it cost them 4 % when it was a runtime branch)
+template <bool GATHER>
 __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lane, const float* cur,
                                                 const float* prev, bool has_prev, long long row) {
-  const int nb = p.n_bands, nx = p.n_extra;
-  const bool mc = p.multicast != 0;
+  const int nb = p.n_bands, nx = GATHER ? p.n_extra : 0;
+  const bool mc = GATHER && p.multicast != 0;
   if (p.out_log) {
     float* o = p.out_log + row * p.ld_log;
     if (mc) for (int b = lane; b < nb; b += 32) mc_store(o + b, cur[b]);
@@ -272,6 +275,7 @@ __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lan
 }
 
 // phase C of one round: max-filter + lagged difference + flux of its frames, coalesced row stores
+template <bool GATHER>
 __device__ __forceinline__ void round_difference(const FrontendParams& p, const RoundDesc* Dc, const float* s_ring,
                                                  int gwarp, int GW, int lane, bool want_diff) {
   const int nb = p.n_bands, R = p.ring_rows, nfr = Dc->nfr, slot0 = Dc->slot0;
@@ -282,12 +286,12 @@ __device__ __forceinline__ void round_difference(const FrontendParams& p, const 
     int sc = slot0 + fi; while (sc >= R) sc -= R;
     int sp = sc - p.diff_frames; if (sp < 0) sp += R;
     const bool has_prev = want_diff && (g - p.diff_frames) >= 0;       // first d rows of a signal are zero
-    warp_difference(p, lane, s_ring + sc * nb, s_ring + sp * nb, has_prev, row0 + g);
+    warp_difference<GATHER>(p, lane, s_ring + sc * nb, s_ring + sp * nb, has_prev, row0 + g);
   }
 }
 
 // ---------------------------------------------------------------------------------------------- the kernel
-template <int N, typename S>
+template <int N, typename S, bool GATHER>
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const FrontendParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int K = N / 2;
@@ -361,7 +365,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   if (pending) {                                                                                       \
     mbar_wait(ring_bar, ring_phase);                                                                   \
     ring_phase ^= 1;                                                                                   \
-    round_difference(p, &G->desc[(r + 3) & 3], s_ring, gwarp, GW, lane, want_diff);                     \
+    round_difference<GATHER>(p, &G->desc[(r + 3) & 3], s_ring, gwarp, GW, lane, want_diff);             \
     pending = false;                                                                                   \
   }
 #define MMB_ROWS_WRITTEN()                                                                             \
@@ -525,7 +529,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
 // ---------------------------------------------------------------------------------------------- host launchers
 template <int N, typename S>
 static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-  frontend_kernel<N, S><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
+  if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
+  else frontend_kernel<N, S, false><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
   return cudaGetLastError();
 }
 
@@ -545,7 +550,10 @@ cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, in
 
 template <int N, typename S>
 static cudaError_t set_one(int smem_bytes) {
-  return cudaFuncSetAttribute(frontend_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       smem_bytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(frontend_kernel<N, S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
 }
 
 // opt the kernel variant in to `smem_bytes` of dynamic shared memory (once per plan)

@@ -291,7 +291,9 @@ __device__ __forceinline__ void round_difference(const FrontendParams& p, const 
 }
 
 // ---------------------------------------------------------------------------------------------- the kernel
-template <int N, typename S, bool GATHER>
+// SPECOUT: the launch may write per-bin outputs (stft, spec, lgd).  Launches that only produce band outputs are a
+// separate instantiation without the emitting copies of the splits.
+template <int N, typename S, bool GATHER, bool SPECOUT>
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const FrontendParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int K = N / 2;
@@ -438,7 +440,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
           oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
           ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
-          if (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row) split_1024x2(lane, v, ex, oa, ob, haveB);
+          if (SPECOUT && (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row)) split_1024x2(lane, v, ex, oa, ob, haveB);
           else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
         }
         if (nb > 0) {
@@ -477,10 +479,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
         o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
         o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
-        if (p.out_lgd && emit) {
+        if (SPECOUT && p.out_lgd && emit) {
           if (o.stft_row || o.spec_row) split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
           else split_2048_lgd(lane, v, ex, s_tw2k, quiet(o), p.out_lgd + row * p.ld_lgd, sgn_odd);
-        } else if (o.stft_row || o.spec_row) {
+        } else if (SPECOUT && (o.stft_row || o.spec_row)) {
           split_2048(lane, v, ex, s_tw2k, o);
         } else {
           split_2048(lane, v, ex, s_tw2k, quiet(o));
@@ -504,7 +506,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
           o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
           o.mag = c == 0 ? my_mag_even : my_mag;
-          if (o.stft_row || o.spec_row) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
+          if (SPECOUT && (o.stft_row || o.spec_row)) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
           else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
           __syncwarp();
         }
@@ -529,8 +531,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
 // ---------------------------------------------------------------------------------------------- host launchers
 template <int N, typename S>
 static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-  if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
-  else frontend_kernel<N, S, false><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
+  const bool specout = p.out_stft || p.out_spec || p.out_lgd;
+  if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true, false><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
+  else if (specout) frontend_kernel<N, S, false, true><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
+  else frontend_kernel<N, S, false, false><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
   return cudaGetLastError();
 }
 
@@ -550,10 +554,13 @@ cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, in
 
 template <int N, typename S>
 static cudaError_t set_one(int smem_bytes) {
-  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       smem_bytes);
+  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false, false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(frontend_kernel<N, S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  e = cudaFuncSetAttribute(frontend_kernel<N, S, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(frontend_kernel<N, S, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              smem_bytes);
 }
 
 // opt the kernel variant in to `smem_bytes` of dynamic shared memory (once per plan)

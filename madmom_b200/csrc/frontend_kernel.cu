@@ -291,9 +291,10 @@ __device__ __forceinline__ void round_difference(const FrontendParams& p, const 
 }
 
 // ---------------------------------------------------------------------------------------------- the kernel
-// SPECOUT: the launch may write per-bin outputs (stft, spec, lgd).  Launches that only produce band outputs are a
+// SPECOUT: per-bin outputs the launch may write: 0 none, 1 stft / spec, 2 lgd (N = 2048), 3 all of them.  Each
+// value is its own instantiation, so that e.g. launches that only produce band outputs are a
 // separate instantiation without the emitting copies of the splits.
-template <int N, typename S, bool GATHER, bool SPECOUT>
+template <int N, typename S, bool GATHER, int SPECOUT>
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const FrontendParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int K = N / 2;
@@ -440,7 +441,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
           oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
           ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
-          if (SPECOUT && (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row)) split_1024x2(lane, v, ex, oa, ob, haveB);
+          if ((SPECOUT & 1) && (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row)) split_1024x2(lane, v, ex, oa, ob, haveB);
           else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
         }
         if (nb > 0) {
@@ -479,10 +480,11 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
         o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
         o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
-        if (SPECOUT && p.out_lgd && emit) {
-          if (o.stft_row || o.spec_row) split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
+        if ((SPECOUT & 2) && p.out_lgd && emit) {
+          if ((SPECOUT & 1) && (o.stft_row || o.spec_row))
+            split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
           else split_2048_lgd(lane, v, ex, s_tw2k, quiet(o), p.out_lgd + row * p.ld_lgd, sgn_odd);
-        } else if (SPECOUT && (o.stft_row || o.spec_row)) {
+        } else if ((SPECOUT & 1) && (o.stft_row || o.spec_row)) {
           split_2048(lane, v, ex, s_tw2k, o);
         } else {
           split_2048(lane, v, ex, s_tw2k, quiet(o));
@@ -506,7 +508,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
           o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
           o.mag = c == 0 ? my_mag_even : my_mag;
-          if (SPECOUT && (o.stft_row || o.spec_row)) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
+          if ((SPECOUT & 1) && (o.stft_row || o.spec_row)) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
           else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
           __syncwarp();
         }
@@ -531,10 +533,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
 // ---------------------------------------------------------------------------------------------- host launchers
 template <int N, typename S>
 static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-  const bool specout = p.out_stft || p.out_spec || p.out_lgd;
-  if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true, false><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
-  else if (specout) frontend_kernel<N, S, false, true><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
-  else frontend_kernel<N, S, false, false><<<grid, p.warps * 32, smem_bytes, stream>>>(p);
+  const bool bins = p.out_stft || p.out_spec, lgd = p.out_lgd != nullptr;
+  const int threads = p.warps * 32;
+  if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true, 0><<<grid, threads, smem_bytes, stream>>>(p);
+  else if (N == 2048 && lgd && bins) frontend_kernel<N, S, false, (N == 2048 ? 3 : 1)><<<grid, threads, smem_bytes, stream>>>(p);
+  else if (N == 2048 && lgd) frontend_kernel<N, S, false, (N == 2048 ? 2 : 0)><<<grid, threads, smem_bytes, stream>>>(p);
+  else if (bins) frontend_kernel<N, S, false, 1><<<grid, threads, smem_bytes, stream>>>(p);
+  else frontend_kernel<N, S, false, 0><<<grid, threads, smem_bytes, stream>>>(p);
   return cudaGetLastError();
 }
 
@@ -554,13 +559,13 @@ cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, in
 
 template <int N, typename S>
 static cudaError_t set_one(int smem_bytes) {
-  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false, false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(frontend_kernel<N, S, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(frontend_kernel<N, S, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              smem_bytes);
+  const cudaFuncAttribute a = cudaFuncAttributeMaxDynamicSharedMemorySize;
+  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false, 0>, a, smem_bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<N, S, false, 1>, a, smem_bytes);
+  if (e == cudaSuccess && N == 2048) e = cudaFuncSetAttribute(frontend_kernel<N, S, false, (N == 2048 ? 2 : 0)>, a, smem_bytes);
+  if (e == cudaSuccess && N == 2048) e = cudaFuncSetAttribute(frontend_kernel<N, S, false, (N == 2048 ? 3 : 1)>, a, smem_bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<N, S, true, 0>, a, smem_bytes);
+  return e;
 }
 
 // opt the kernel variant in to `smem_bytes` of dynamic shared memory (once per plan)

@@ -176,7 +176,10 @@ def complex_flux_batch(fe, pcm, lengths, temporal_filter=3, scratch_bytes=None):
     hi = torch.from_numpy(np.minimum(starts.astype(np.int64) + lens + 1, fb.shape[0]).astype(np.int32)).to(dev)
     K, B = plan.num_bins, plan.num_bands
     max_rows = max(int(scratch_bytes // (4 * (K + B))), max(T) if T else 1)
-    lgd = diff = None
+    # the scratch matrices stay with the front end between calls (no multi-GiB allocation in the steady state)
+    lgd, diff = getattr(fe, "_cf_scratch", (None, None))
+    if lgd is not None and (lgd.device != dev or lgd.shape[1] != K or diff.shape[1] != B):
+        lgd = diff = None
     i0, row0 = 0, 0
     while i0 < len(T):
         i1, rows = i0, 0
@@ -184,8 +187,11 @@ def complex_flux_batch(fe, pcm, lengths, temporal_filter=3, scratch_bytes=None):
             rows += T[i1]
             i1 += 1
         if lgd is None or lgd.shape[0] < rows:
+            lgd = diff = None
+            fe._cf_scratch = (None, None)
             lgd = torch.empty((max(rows, 1), K), dtype=torch.float32, device=dev)
             diff = torch.empty((max(rows, 1), B), dtype=torch.float32, device=dev)
+            fe._cf_scratch = (lgd, diff)
         units = _lib.make_units(lengths[i0:i1], T[i0:i1], pcm_offsets=offsets[i0:i1])
         plan.run(pcm, units, {"lgd": lgd[:rows], "diff": diff[:rows]})
         seg = torch.from_numpy(np.concatenate(([0], np.cumsum(T[i0:i1]))).astype(np.int64)).to(dev)

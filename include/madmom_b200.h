@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define MMB_VERSION 100 /* 0.1.0 */
+#define MMB_VERSION 101 /* 0.1.1: mmb_run_gather, mmb_run_multicast */
 
 #if defined(__GNUC__)
 #define MMB_API __attribute__((visibility("default")))

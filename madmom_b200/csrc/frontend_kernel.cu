@@ -65,6 +65,11 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 template <int N, typename S>
 __device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, int fpr, int vid, int vstride) {
   const int lead = ((p.out_diff != nullptr) || (p.out_odf != nullptr)) ? p.diff_frames : 0;
+  // ring slots rotate from round to round, across chunk changes too: a round takes the slots behind those of the
+  // round before it, so the rows a pending phase C still needs are never the ones being written (the ring holds two
+  // rounds + d rows) and a new chunk needs neither a drain nor a barrier
+  int slot = first ? 0 : d.slot0 + d.nfr;
+  if (slot >= p.ring_rows) slot -= p.ring_rows;
   long long g0;
   bool new_chunk = first;
   int chunk = first ? vid : d.chunk;
@@ -98,7 +103,7 @@ __device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, in
   const long long s_end = frame_start_sample(g0 + d.nfr - 1, p.hop, N, p.origin) + N;
   d.span = (int)(s_end - d.s_begin);
   d.l0 = d.s_begin - d.sample_base;
-  d.slot0 = (int)(g0 % (long long)p.ring_rows);
+  d.slot0 = slot;
   // bulk staging: every staged sample is a real sample of the unit and the 16-byte aligned hull stays inside
   // the PCM buffer
   constexpr int A = 16 / (int)sizeof(S);
@@ -358,7 +363,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
   const float sgn_odd = p.circular_shift ? -1.0f : 1.0f;
   const int R = p.ring_rows;
   uint32_t pcm_phase = 0, ring_phase = 0;   // parities of the next completions of the group's two mbarriers
-  int prev_chunk = -1;
   bool pending = false;                     // phase C of the previous round is still to be done by this warp
 
   // Phase C of round r-1 is deferred until this warp is about to write its ring row of round r: by then every
@@ -385,12 +389,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     const RoundDesc* D = &G->desc[r & 3];
     const int nfr = D->nfr;
     if (nfr == 0) break;
-    // a new chunk maps its frames to unrelated ring slots: finish the previous chunk first
-    if (D->chunk != prev_chunk) {
-      MMB_PENDING_DIFFERENCE();
-      if (r > 0) group_sync(grp, gthreads);
-      prev_chunk = D->chunk;
-    }
     // ---- spans that touch the edge of a signal are filled here with zero padding (all warps have read the
     //      previous span: the descriptor is written by the last of them)
     if (!D->bulk) {

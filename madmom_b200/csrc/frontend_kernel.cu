@@ -209,8 +209,18 @@ __device__ __forceinline__ void warp_band_epilogue(const FrontendParams& p, int 
                                                    float* ring_row, long long row, bool emit) {
   const int nb = p.n_bands, bp = p.b_pad, nq = p.max_q;
   for (int b = lane; b < nb; b += 32) {
-    float acc = part[b];
-    for (int q = 1; q < nq; ++q) acc += part[q * bp + b];     // slots without a piece stay zero
+    // pieces are added in order q = 0, 1, ...; slots without a piece stay zero.  The first four loads are issued
+    // together (the piece count is warp-uniform), the rare longer tails in a loop.
+    const float* pp = part + b;
+    const float a0 = pp[0];
+    const float a1 = nq > 1 ? pp[bp] : 0.0f;
+    const float a2 = nq > 2 ? pp[2 * bp] : 0.0f;
+    const float a3 = nq > 3 ? pp[3 * bp] : 0.0f;
+    float acc = a0;
+    if (nq > 1) acc += a1;
+    if (nq > 2) acc += a2;
+    if (nq > 3) acc += a3;
+    for (int q = 4; q < nq; ++q) acc += pp[q * bp];
     if (emit && p.out_filt) p.out_filt[row * p.ld_filt + b] = acc;
     ring_row[b] = p.log_mode != 0 ? log_scaled(acc, p.log_mode, p.mul, p.add) : acc;
   }

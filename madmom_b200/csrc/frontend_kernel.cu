@@ -180,21 +180,33 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
     const float* m0 = SPLIT ? ((st & 1) ? mag1 + (st >> 1) : mag0 + (st >> 1)) : mag0 + st;
     const float* m1 = SPLIT ? ((st & 1) ? mag0 + ((st + 1) >> 1) : mag1 + (st >> 1)) : ((NF == 2) ? mag1 + st : mag0);
     float2 acc0 = make_float2(0.0f, 0.0f), acc1 = make_float2(0.0f, 0.0f);    // (even taps, odd taps), two frames
-#pragma unroll 1
-    for (int i = 0; i < fp.iters; i += 4) {          // pass lengths are multiples of four (capi.cu)
-      const float4 wv = *w;                          // taps i .. i+3 of this lane
+    // four taps of this lane per group (pass lengths are multiples of four, capi.cu); groups are taken two at a time
+    // (an odd one first) so that the loop overhead is paid once per eight taps; the order of the FMAs is unchanged
+    constexpr int MS = SPLIT ? 2 : 4;                // magnitudes a group advances in each array
+    auto group = [&](int g) {
+      const float4 wv = w[32 * g];                   // taps 4 g .. 4 g + 3 of this lane
       const float2 w01 = make_float2(wv.x, wv.y), w23 = make_float2(wv.z, wv.w);
-      const float x0 = m0[0], x1 = SPLIT ? m1[0] : m0[1], x2 = SPLIT ? m0[1] : m0[2], x3 = SPLIT ? m1[1] : m0[3];
+      const float* a = m0 + MS * g;
+      const float* b = m1 + MS * g;
+      const float x0 = a[0], x1 = SPLIT ? b[0] : a[1], x2 = SPLIT ? a[1] : a[2], x3 = SPLIT ? b[1] : a[3];
       acc0 = fma2(make_float2(x0, x1), w01, acc0);   // packed pairs: same per-half FMA chains as the scalar form
       acc0 = fma2(make_float2(x2, x3), w23, acc0);
-      if (SPLIT) { m0 += 2; m1 += 2; w += 32; continue; }
-      if (NF == 2) {
-        const float y0 = m1[0], y1 = m1[1], y2 = m1[2], y3 = m1[3];
+      if (!SPLIT && NF == 2) {
+        const float y0 = b[0], y1 = b[1], y2 = b[2], y3 = b[3];
         acc1 = fma2(make_float2(y0, y1), w01, acc1);
         acc1 = fma2(make_float2(y2, y3), w23, acc1);
-        m1 += 4;
       }
-      w += 32; m0 += 4;
+    };
+    const int n4 = fp.iters >> 2;
+    if (n4 & 1) {
+      group(0);
+      w += 32; m0 += MS; if (SPLIT || NF == 2) m1 += MS;
+    }
+#pragma unroll 1
+    for (int k = n4 >> 1; k > 0; --k) {
+      group(0);
+      group(1);
+      w += 64; m0 += 2 * MS; if (SPLIT || NF == 2) m1 += 2 * MS;
     }
     const float a0 = acc0.x, c0 = acc0.y, a1 = acc1.x, c1 = acc1.y;
     const int pid = s_pid[ps * 32 + lane];

@@ -13,6 +13,7 @@
 
 #include "../../include/madmom_b200.h"
 #include "frontend_params.h"
+#include "fft_core.cuh"          // tw1_index: layout of the inter-pass twiddle table
 
 using mmb::FrontendParams;
 using mmb::Track;
@@ -274,7 +275,7 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   for (int k1 = 0; k1 < 32; ++k1)
     for (int l = 0; l < 32; ++l) {
       const double a = -2.0 * PI * (double)((l * k1) % 1024) / 1024.0;
-      tw1[k1 * 32 + l] = make_float2((float)std::cos(a), (float)std::sin(a));
+      tw1[mmb::tw1_index(k1, l)] = make_float2((float)std::cos(a), (float)std::sin(a));
     }
   for (int k = 0; k < 1024; ++k) {
     const double a = -2.0 * PI * (double)k / 2048.0;

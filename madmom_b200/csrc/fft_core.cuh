@@ -11,7 +11,7 @@
 //
 // Decomposition (Cooley-Tukey, n = 32*n1 + n2, k = k1 + 32*k2, lane = n2 in pass 1, lane = k1 in pass 2):
 //   pass 1  A_l[k1]   = sum_n1 z[32 n1 + l] W32^(n1 k1)            32-point FFT in registers
-//   twiddle A_l[k1]  *= W1024^(l k1)                               table T1[k1][l]   (conflict-free LDS.64)
+//   twiddle A_l[k1]  *= W1024^(l k1)                               table T1 (tw1_index: k1 and k1 + 16 in one LDS.128)
 //   xchg    B_j[n2]   = A_n2[j]                                    32x33 float2 transpose through smem
 //   pass 2  Z[j+32k2] = sum_n2 B_j[n2] W32^(n2 k2)                 32-point FFT in registers
 // The in-register FFT is a fully unrolled radix-2 DIF (natural in, bit-reversed out); the bit reversal is
@@ -166,16 +166,27 @@ MMB_HD void fft32_dif(float2 (&v)[32]) {
 
 MMB_HD float2 cmul(float2 a, float2 w) { return make_float2(a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x); }
 
+// Layout of the inter-pass twiddle table: W1024^(lane k1) and W1024^(lane (k1 + 16)) sit side by side, so that the
+// two twiddles of the register pair (r, r + 1) (k1 = brev5(r) < 16 and k1 + 16) arrive with one 16-byte load.
+MMB_HD constexpr int tw1_index(int k1, int lane) { return ((k1 & 15) * 32 + lane) * 2 + (k1 >> 4); }
+
 // ---- the four phases of the 1024-point warp FFT -------------------------------------------------------
 // phase 1: in-register FFT over n1, inter-pass twiddle, store into the exchange tile (row k1, column lane)
 MMB_HD void core_pass1(int lane, float2 (&v)[32], float2* ex, const float2* __restrict__ tw1) {
   fft32_dif(v);
 #pragma unroll
-  for (int r = 0; r < 32; ++r) {
-    const int k1 = brev5(r);
+  for (int r = 0; r < 32; r += 2) {
+    const int k1 = brev5(r);                        // < 16; register r + 1 holds k1 + 16
+#if defined(__CUDA_ARCH__)
+    const float4 t = reinterpret_cast<const float4*>(tw1)[k1 * 32 + lane];
+    const float2 ta = make_float2(t.x, t.y), tb = make_float2(t.z, t.w);
+#else
+    const float2 ta = tw1[tw1_index(k1, lane)], tb = tw1[tw1_index(k1 + 16, lane)];
+#endif
     float2 a = v[r];
-    if (k1 != 0) a = cmul(a, tw1[k1 * 32 + lane]);
+    if (k1 != 0) a = cmul(a, ta);
     ex[k1 * kExStride + lane] = a;
+    ex[(k1 + 16) * kExStride + lane] = cmul(v[r + 1], tb);
   }
 }
 // phase 2 (after __syncwarp): load row `lane` of the tile, FFT over n2.  v[r] = Z[lane + 32*brev5(r)].

@@ -54,7 +54,7 @@ struct FrontendParams {
   SmemLayout L;
   // plan constants (device)
   const float* win;              // N floats, fft_window * 0.5
-  const float2* tw1;             // 1024: W1024^(l*k1) at [k1*32 + l]
+  const float2* tw1;             // 1024: W1024^(l*k1) at [tw1_index(k1, l)] (fft_core.cuh)
   const float2* tw2k;            // 1024: W2048^k (N = 2048 uses the first 512)
   const float2* tw4k;            // 512 : W4096^(2j+1)
   int32_t n_bands;               // 0 -> no filterbank stage

@@ -19,7 +19,7 @@ static void make_tables(std::vector<float2>& tw1, std::vector<float2>& tw2k, std
   for (int k1 = 0; k1 < 32; ++k1)
     for (int l = 0; l < 32; ++l) {
       double a = -2.0 * PI * (double)(l * k1) / 1024.0;
-      tw1[k1 * 32 + l] = make_float2((float)cos(a), (float)sin(a));
+      tw1[tw1_index(k1, l)] = make_float2((float)cos(a), (float)sin(a));
     }
   for (int k = 0; k < 1024; ++k) {   // index q*32 + lane == k
     double a = -2.0 * PI * (double)k / 2048.0;

@@ -52,3 +52,28 @@ def test_shard_arithmetic():
     # more ranks than frames: trailing ranks are empty but still contribute padded rows
     sh = parallel.frame_shards(1000, 441., 2048, 4, 0, 1)
     assert [s.frame_count for s in sh] == [1, 1, 1, 0]
+
+
+def test_frame_shards_for_paired_frames():
+    """frame_size 1024: the kernel packs frames (2m, 2m + 1) into one FFT, so every range starts at an even frame
+    (range size rounded up to even) and the left halo reaches one frame further back than diff_frames alone needs;
+    the ranges still cover every frame exactly once."""
+    from madmom_b200 import parallel, recipe as R
+    n, hop, d = 44100 * 61 + 123, 441., 1
+    T = R.num_frames(n, hop)
+    for world in (2, 3, 5, 8):
+        sh = parallel.frame_shards(n, hop, 1024, world, 0, d)
+        per = sh[0].rows_per_rank
+        assert per % 2 == 0 and per * world >= T and (per - 2) * world < T + 2 * world
+        assert sum(s.frame_count for s in sh) == T
+        at = 0
+        for s in sh:
+            if s.frame_count == 0:
+                continue
+            assert s.frame_first == at and s.frame_first % 2 == 0
+            at += s.frame_count
+            lead = max(s.frame_first - d - 1, 0)
+            assert s.sample_lo == max(R.frame_start(lead, 1024, hop, 0), 0)
+            assert s.sample_hi == min(R.frame_start(s.frame_first + s.frame_count - 1, 1024, hop, 0) + 1024, n)
+        # the other frame sizes keep the plain ceil(T / world) split
+        assert parallel.frame_shards(n, hop, 2048, world, 0, d)[0].rows_per_rank == -(-T // world)

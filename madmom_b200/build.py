@@ -11,7 +11,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIBPATH = os.path.join(LIBDIR, "libmadmom_b200.so")
-SOURCES = ["frontend_kernel.cu", "capi.cu", "peaks.cu", "postproc.cu"]
+# (source, object name, extra flags): the front-end kernel is compiled once per frame size, in parallel
+SOURCES = [("frontend_kernel.cu", "frontend_kernel_%d.o" % n, ["-DMMB_FRONTEND_N=%d" % n]) for n in (2048, 4096, 1024)]
+SOURCES += [("frontend_dispatch.cu", "frontend_dispatch.o", ["-DMMB_SPLIT_FRONTEND"]), ("capi.cu", "capi.o", []),
+            ("peaks.cu", "peaks.o", []), ("postproc.cu", "postproc.o", [])]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 
@@ -46,9 +49,10 @@ def build_library(force=False, verbose=False):
     nvcc = _nvcc()
     objs = []
     procs = []
-    for src in SOURCES:
-        obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+    for src, objname, extra in SOURCES:
+        obj = os.path.join(objdir, objname)
+        cmd = ([nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) +
+               ["-c", os.path.join(CSRC, src), "-o", obj])
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     for cmd, pr in procs:

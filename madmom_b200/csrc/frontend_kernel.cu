@@ -563,6 +563,18 @@ static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes,
   return cudaGetLastError();
 }
 
+#if defined(MMB_FRONTEND_N)
+// One frame size per translation unit (madmom_b200/build.py compiles this file three times in parallel with
+// -DMMB_FRONTEND_N=1024 / 2048 / 4096; frontend_dispatch.cu routes launch_frontend / frontend_set_smem to them).
+#define MMB_CAT2(a, b) a##b
+#define MMB_CAT(a, b) MMB_CAT2(a, b)
+cudaError_t MMB_CAT(launch_frontend_, MMB_FRONTEND_N)(int sample_bytes, const FrontendParams& p, int grid,
+                                                      int smem_bytes, cudaStream_t stream) {
+  if (sample_bytes == 2) return launch_one<MMB_FRONTEND_N, int16_t>(p, grid, smem_bytes, stream);
+  if (sample_bytes == 4) return launch_one<MMB_FRONTEND_N, float>(p, grid, smem_bytes, stream);
+  return cudaErrorInvalidValue;
+}
+#else
 cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, int grid, int smem_bytes,
                             cudaStream_t stream) {
   if (sample_bytes == 2) {
@@ -577,6 +589,8 @@ cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, in
   return cudaErrorInvalidValue;
 }
 
+#endif
+
 template <int N, typename S>
 static cudaError_t set_one(int smem_bytes) {
   const cudaFuncAttribute a = cudaFuncAttributeMaxDynamicSharedMemorySize;
@@ -588,6 +602,13 @@ static cudaError_t set_one(int smem_bytes) {
   return e;
 }
 
+#if defined(MMB_FRONTEND_N)
+cudaError_t MMB_CAT(frontend_set_smem_, MMB_FRONTEND_N)(int sample_bytes, int smem_bytes) {
+  if (sample_bytes == 2) return set_one<MMB_FRONTEND_N, int16_t>(smem_bytes);
+  if (sample_bytes == 4) return set_one<MMB_FRONTEND_N, float>(smem_bytes);
+  return cudaErrorInvalidValue;
+}
+#else
 // opt the kernel variant in to `smem_bytes` of dynamic shared memory (once per plan)
 cudaError_t frontend_set_smem(int N, int sample_bytes, int smem_bytes) {
   if (sample_bytes == 2) {
@@ -601,5 +622,7 @@ cudaError_t frontend_set_smem(int N, int sample_bytes, int smem_bytes) {
   }
   return cudaErrorInvalidValue;
 }
+
+#endif
 
 }  // namespace mmb

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define MMB_VERSION 101 /* 0.1.1: mmb_run_gather, mmb_run_multicast */
+#define MMB_VERSION 102 /* 0.1.2: float64 stft / spec outputs, include_nyquist, mmb_run_multi, PCM gain */
 
 #if defined(__GNUC__)
 #define MMB_API __attribute__((visibility("default")))
@@ -70,6 +70,8 @@ typedef struct mmb_config {
   int32_t positive_diffs;
   int32_t chunk_frames;    /* output frames per work chunk, 0 = library default                            */
   int32_t device;          /* CUDA device ordinal                                                          */
+  int32_t include_nyquist; /* stft / spec rows carry frame_size/2 + 1 bins (stft.py:93-95); plans without a
+                              filterbank only                                                               */
 } mmb_config;
 
 /* One independent unit of work: a whole track (sample_base = frame_first = 0, pcm_len = num_samples) or a
@@ -89,8 +91,9 @@ typedef struct mmb_track {
  * hstack((spec, diff)) of SpectrogramDifferenceProcessor(stack_diffs=np.hstack) is log = base,
  * diff = base + num_bands, both with ld = row length of the stacked matrix. */
 typedef struct mmb_outputs {
-  void* stft;  int64_t ld_stft;  /* complex64 (rows, frame_size/2)              */
-  float* spec; int64_t ld_spec;  /* magnitudes (rows, frame_size/2)             */
+  void* stft;  int64_t ld_stft;  /* complex64 (rows, frame_size/2 [+ 1 with include_nyquist]): float64 FFT rounded
+                                    once, like the reference (stft.py:26, :105-131)                             */
+  float* spec; int64_t ld_spec;  /* magnitudes of those complex64 bins (rows, same width)                        */
   float* filt; int64_t ld_filt;  /* filtered, before log (rows, num_bands)      */
   float* log;  int64_t ld_log;   /* log-filtered spectrogram (rows, num_bands)  */
   float* diff; int64_t ld_diff;  /* (positive, max-filtered) difference         */

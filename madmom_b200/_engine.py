@@ -54,10 +54,11 @@ def _filterbank_key(fb):
 class Chain(object):
     """Everything that defines the numbers of one chain; hashable into a plan key."""
 
-    def __init__(self, frames, window=np.hanning, circular_shift=False, fft_window=None):
+    def __init__(self, frames, window=np.hanning, circular_shift=False, fft_window=None, include_nyquist=False):
         self.frames = frames
         self.window = window
         self.circular_shift = bool(circular_shift)
+        self.include_nyquist = bool(include_nyquist)
         self.fft_window = fft_window            # float64 array actually multiplied onto the samples
         self.filterbank = None
         self.log_mode, self.mul, self.add = _lib.LOG_NONE, 1.0, 0.0
@@ -80,7 +81,7 @@ class Chain(object):
         fb = self.filterbank
         key = (device, fr.frame_size, fr.hop_size, dtype.str, self.circular_shift, fw.tobytes(),
                _filterbank_key(fb), self.log_mode, float(self.mul),
-               float(self.add), self.diff_frames, self.diff_max_bins, self.positive_diffs)
+               float(self.add), self.diff_frames, self.diff_max_bins, self.positive_diffs, self.include_nyquist)
         with _lock:
             plan = _plans.get(key)
             if plan is None:
@@ -91,7 +92,7 @@ class Chain(object):
                                          circular_shift=self.circular_shift, filterbank=fb, log_mode=self.log_mode,
                                          mul=self.mul, add=self.add, diff_frames=self.diff_frames,
                                          diff_max_bins=self.diff_max_bins, positive_diffs=self.positive_diffs,
-                                         device=device)
+                                         device=device, include_nyquist=self.include_nyquist)
                 _plans[key] = plan
         return plan
 

@@ -22,7 +22,7 @@ class Config(ctypes.Structure):
                 ("num_bands", c_i32), ("band_start", ctypes.POINTER(c_i32)), ("band_len", ctypes.POINTER(c_i32)),
                 ("band_weights", ctypes.POINTER(c_f32)), ("log_mode", c_i32), ("mul", c_f32), ("add", c_f32),
                 ("diff_frames", c_i32), ("diff_max_bins", c_i32), ("positive_diffs", c_i32),
-                ("chunk_frames", c_i32), ("device", c_i32)]
+                ("chunk_frames", c_i32), ("device", c_i32), ("include_nyquist", c_i32)]
 
 
 class Track(ctypes.Structure):
@@ -171,13 +171,13 @@ class FrontEndPlan(object):
 
     def __init__(self, frame_size, hop_size, fft_window, pcm_dtype=np.int16, origin=0, circular_shift=False,
                  filterbank=None, log_mode=LOG_NONE, mul=1.0, add=0.0, diff_frames=0, diff_max_bins=0,
-                 positive_diffs=False, chunk_frames=0, device=0):
+                 positive_diffs=False, chunk_frames=0, device=0, include_nyquist=False):
         lib = load()
         self._lib = lib
         self._handle = c_vp()
         self._layouts = {}
         self.frame_size, self.hop_size, self.origin = int(frame_size), float(hop_size), int(origin)
-        self.num_bins = self.frame_size // 2
+        self.num_bins = self.frame_size // 2 + (1 if include_nyquist else 0)
         self.device = int(device)
         pcm_dtype = np.dtype(pcm_dtype)
         if pcm_dtype == np.int16:
@@ -193,6 +193,7 @@ class FrontEndPlan(object):
         cfg = Config()
         cfg.frame_size, cfg.pcm_dtype, cfg.hop_size, cfg.origin = self.frame_size, code, self.hop_size, self.origin
         cfg.circular_shift = int(bool(circular_shift))
+        cfg.include_nyquist = int(bool(include_nyquist))
         cfg.fft_window = win.ctypes.data_as(ctypes.POINTER(c_f64))
         keep = [win]
         if filterbank is not None:

@@ -51,6 +51,36 @@ def rescale(signal, dtype=np.float32):
     return signal.astype(dtype) / np.iinfo(signal.dtype).max
 
 
+def _db_to_factor(gain):
+    """dB -> amplitude factor as the reference spells it: sqrt(10) ** (gain / 10) (madmom/audio/signal.py:96)."""
+    return np.power(np.sqrt(10.), 0.1 * gain)
+
+
+def adjust_gain(signal, gain):
+    """Scale by `gain` dB and cast back to the input dtype (integer PCM truncates towards zero); amplifying integer
+    PCM is refused because it could clip (madmom/audio/signal.py:71-104)."""
+    factor = _db_to_factor(gain)
+    if factor > 1 and np.issubdtype(signal.dtype, np.integer):
+        raise ValueError("positive gain adjustments are only supported for float dtypes.")
+    return np.asanyarray(signal * factor, dtype=signal.dtype)
+
+
+def attenuate(signal, attenuation):
+    """`adjust_gain` by -attenuation dB; 0 dB returns the signal itself (madmom/audio/signal.py:107-131)."""
+    return signal if attenuation == 0 else adjust_gain(signal, -attenuation)
+
+
+def normalize(signal):
+    """Scale to the full range of the dtype: floats to [-1, 1], int16 / int32 to +-iinfo.max; same dtype out
+    (madmom/audio/signal.py:134-167)."""
+    scaling = float(np.max(np.abs(signal)))
+    if np.issubdtype(signal.dtype, np.integer):
+        if signal.dtype not in (np.int16, np.int32):
+            raise ValueError("only float and np.int16/32 dtypes supported, not %s." % signal.dtype)
+        scaling /= np.iinfo(signal.dtype).max
+    return np.asanyarray(signal / scaling, dtype=signal.dtype)
+
+
 def remix(signal, num_channels, channel=None):
     """Down-mix to mono (mean over channels cast back to the input dtype) or up-mix mono by repetition
     (madmom/audio/signal.py:170-223)."""
@@ -80,8 +110,10 @@ class Signal(np.ndarray):
             data.sample_rate = sample_rate
         if num_channels:
             data = remix(data, num_channels, channel).view(cls)
-        if norm or (gain is not None and gain != 0):
-            raise NotImplementedError("norm / gain are outside the GPU front end; scale the samples beforehand")
+        if norm:
+            data = normalize(data)
+        if gain is not None and gain != 0:
+            data = adjust_gain(data, gain)
         if sample_rate is not None and data.sample_rate is not None and sample_rate != data.sample_rate:
             raise NotImplementedError("re-sampling is outside the GPU front end")
         if data.sample_rate is None:

@@ -39,15 +39,30 @@ class Spectrogram(DeviceResult):
     _output = "spec"
 
     def __init__(self, stft, **kwargs):
+        self._source = None
         if isinstance(stft, Spectrogram):
-            stft = stft.stft
+            # already a Spectrogram (of any stage): the reference keeps the given data and only re-types it
+            # (madmom/audio/spectrogram.py:125-127), so a filtered / logarithmic / difference matrix stays what it is
+            DeviceResult.__init__(self, stft._chain.copy())
+            self._source = stft
+            self._output = stft._output
+            self.stft = stft.stft
+            self.frames = stft.stft.frames
+            return
         if not isinstance(stft, ShortTimeFourierTransform):
             stft = ShortTimeFourierTransform(stft, **kwargs)
         DeviceResult.__init__(self, stft._chain.copy())
         self.stft = stft
         self.frames = stft.frames
 
+    def _compute(self):
+        if getattr(self, "_source", None) is not None:
+            return self._source.tensor
+        return DeviceResult._compute(self)
+
     def _shape(self):
+        if getattr(self, "_source", None) is not None:
+            return self._source.shape
         return self.stft.num_frames, self.stft.num_bins
 
     @property
@@ -88,7 +103,9 @@ class FilteredSpectrogram(Spectrogram):
                  norm_filters=NORM_FILTERS, unique_filters=UNIQUE_FILTERS, **kwargs):
         if not isinstance(spectrogram, Spectrogram):
             spectrogram = Spectrogram(spectrogram, **kwargs)
-        if isinstance(spectrogram, (FilteredSpectrogram, LogarithmicSpectrogram, SpectrogramDifference)):
+        c0 = spectrogram._chain
+        if (isinstance(spectrogram, (FilteredSpectrogram, LogarithmicSpectrogram, SpectrogramDifference)) or
+                c0.filterbank is not None or c0.log_mode != 0 or c0.diff_frames != 0):
             raise NotImplementedError("filtering an already filtered / logarithmic spectrogram is not available "
                                       "on the GPU path")
         if isinstance(filterbank, type) and issubclass(filterbank, Filterbank):
@@ -146,7 +163,8 @@ class LogarithmicSpectrogram(Spectrogram):
     def __init__(self, spectrogram, log=LOG, mul=MUL, add=ADD, **kwargs):
         if not isinstance(spectrogram, Spectrogram):
             spectrogram = Spectrogram(spectrogram, **kwargs)
-        if isinstance(spectrogram, (LogarithmicSpectrogram, SpectrogramDifference)):
+        if (isinstance(spectrogram, (LogarithmicSpectrogram, SpectrogramDifference)) or
+                spectrogram._chain.log_mode != 0 or spectrogram._chain.diff_frames != 0):
             raise NotImplementedError("the logarithm of an already logarithmic spectrogram / a difference is not "
                                       "available on the GPU path")
         DeviceResult.__init__(self, spectrogram._chain.copy())
@@ -241,7 +259,7 @@ class SpectrogramDifference(Spectrogram):
                  positive_diffs=POSITIVE_DIFFS, keep_dims=True, **kwargs):
         if not isinstance(spectrogram, Spectrogram):
             spectrogram = Spectrogram(spectrogram, **kwargs)
-        if isinstance(spectrogram, SpectrogramDifference):
+        if isinstance(spectrogram, SpectrogramDifference) or spectrogram._chain.diff_frames != 0:
             raise NotImplementedError("the difference of a difference is not available on the GPU path")
         if diff_frames is None:
             diff_frames = _diff_frames(diff_ratio, hop_size=spectrogram.stft.frames.hop_size,

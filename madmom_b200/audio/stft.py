@@ -126,22 +126,21 @@ class ShortTimeFourierTransform(DeviceResult):
         frame_size = frames.shape[1]
         if fft_size is not None and fft_size != frame_size:
             raise NotImplementedError("fft_size != frame_size (zero padding) is not available on the GPU path")
-        if include_nyquist:
-            raise NotImplementedError("include_nyquist is not available on the GPU path")
         if frame_size not in (1024, 2048, 4096):
             raise NotImplementedError("frame_size must be 1024, 2048 or 4096 on the GPU path, not %d" % frame_size)
         window = window_of(window, frame_size)
-        chain = Chain(frames, window=window, circular_shift=circular_shift, fft_window=fft_window)
+        chain = Chain(frames, window=window, circular_shift=circular_shift, fft_window=fft_window,
+                      include_nyquist=include_nyquist)
         DeviceResult.__init__(self, chain)
         self.frames = frames
         self.window = window
         self.fft_window = chain.resolved_fft_window()
         self.fft_size = frame_size
         self.circular_shift = bool(circular_shift)
-        self.include_nyquist = False
+        self.include_nyquist = bool(include_nyquist)
 
     def _shape(self):
-        return self.frames.num_frames, self.fft_size >> 1
+        return self.frames.num_frames, self.num_bins
 
     @property
     def dtype(self):
@@ -153,10 +152,12 @@ class ShortTimeFourierTransform(DeviceResult):
 
     @property
     def num_bins(self):
-        return self.fft_size >> 1
+        # stft.py:93-95: fft_size >> 1, plus the Nyquist bin on request
+        return (self.fft_size >> 1) + (1 if self.include_nyquist else 0)
 
     @property
     def bin_frequencies(self):
+        # stft.py:386-389: fft_frequencies(num_bins, sample_rate) with num_bins as stored (Nyquist included)
         return fft_frequencies(self.num_bins, self.frames.signal.sample_rate)
 
     def spec(self, **kwargs):

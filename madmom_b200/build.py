@@ -14,7 +14,8 @@ LIBPATH = os.path.join(LIBDIR, "libmadmom_b200.so")
 # (source, object name, extra flags): the front-end kernel is compiled once per frame size, in parallel
 SOURCES = [("frontend_kernel.cu", "frontend_kernel_%d.o" % n, ["-DMMB_FRONTEND_N=%d" % n]) for n in (2048, 4096, 1024)]
 SOURCES += [("frontend_dispatch.cu", "frontend_dispatch.o", ["-DMMB_SPLIT_FRONTEND"]), ("capi.cu", "capi.o", []),
-            ("peaks.cu", "peaks.o", []), ("postproc.cu", "postproc.o", [])]
+            ("calibration.cu", "calibration.o", []), ("postproc.cu", "postproc.o", []),
+            ("stft64.cu", "stft64.o", [])]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 

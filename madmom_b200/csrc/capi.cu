@@ -79,6 +79,8 @@ struct mmb_plan {
   bool chunk_fixed = false;      // set by the caller / MMB_CHUNK_ROUNDS: never adapted to the size of a launch
   int n_passes = 0, max_q = 0, b_pad = 0, w_floats = 0, fb_iters = 0;
   float* d_win = nullptr;
+  double* d_win64 = nullptr;     // fft_window in float64 and W_N^k, k < N/2: the float64 STFT kernel (stft64.cu)
+  double2* d_tw64 = nullptr;
   float2 *d_tw1 = nullptr, *d_tw2k = nullptr, *d_tw4k = nullptr;
   mmb::FbPass* d_pass = nullptr;
   float* d_fbw = nullptr;
@@ -119,7 +121,7 @@ static cudaError_t upload(T** dst, const std::vector<T>& src) {
 
 extern "C" int mmb_plan_destroy(mmb_plan* p) {
   if (!p) return MMB_OK;
-  cudaFree(p->d_win); cudaFree(p->d_tw1); cudaFree(p->d_tw2k); cudaFree(p->d_tw4k);
+  cudaFree(p->d_win); cudaFree(p->d_win64); cudaFree(p->d_tw64); cudaFree(p->d_tw1); cudaFree(p->d_tw2k); cudaFree(p->d_tw4k);
   cudaFree(p->d_pass); cudaFree(p->d_fbw); cudaFree(p->d_fbstart); cudaFree(p->d_fbpid);
   if (p->pipe) { free_slots(p->pipe->slots, 3); delete p->pipe; }
   delete p;
@@ -243,6 +245,9 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   if (cfg->diff_frames < 0 || cfg->diff_frames > mmb::kMaxDiffFrames)
     return fail(MMB_E_UNSUPPORTED, "diff_frames must be in [0, 16]");
   if (cfg->log_mode < 0 || cfg->log_mode > MMB_LOG_LOG2) return fail(MMB_E_INVALID, "bad log_mode");
+  if (cfg->include_nyquist && cfg->num_bands > 0)
+    return fail(MMB_E_UNSUPPORTED, "include_nyquist is available for the stft / spec outputs only (no filterbank)");
+  if (!(cfg->hop_size < 1e6)) return fail(MMB_E_UNSUPPORTED, "hop_size must be below 1e6 samples");
   const int K = N / 2;
   std::vector<int32_t> woff(cfg->num_bands);
   int nnz = 0;
@@ -255,16 +260,16 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   mmb_plan* p = new (std::nothrow) mmb_plan();
   if (!p) return fail(MMB_E_NOMEM, "out of host memory");
   p->pipe = new (std::nothrow) HostPipe();
-  if (!p->pipe) { delete p; return fail(MMB_E_NOMEM, "out of host memory"); }
+  if (!p->pipe) { mmb_plan_destroy(p); return fail(MMB_E_NOMEM, "out of host memory"); }
   p->cfg = *cfg;
   p->cfg.fft_window = nullptr; p->cfg.band_start = nullptr; p->cfg.band_len = nullptr; p->cfg.band_weights = nullptr;
   p->nnz = nnz;
   p->sample_bytes = cfg->pcm_dtype == MMB_PCM_I16 ? 2 : 4;
   cudaError_t e = cudaSetDevice(cfg->device);
-  if (e != cudaSuccess) { delete p; return cuda_fail(e, "cudaSetDevice"); }
+  if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "cudaSetDevice"); }
   cudaDeviceProp prop;
   e = cudaGetDeviceProperties(&prop, cfg->device);
-  if (e != cudaSuccess) { delete p; return cuda_fail(e, "cudaGetDeviceProperties"); }
+  if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "cudaGetDeviceProperties"); }
   p->num_sms = prop.multiProcessorCount;
 
   // ---- tables (float64 -> float32)
@@ -285,11 +290,18 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
     const double a = -2.0 * PI * (double)(2 * j + 1) / 4096.0;
     tw4k[j] = make_float2((float)std::cos(a), (float)std::sin(a));
   }
+  std::vector<double> win64(cfg->fft_window, cfg->fft_window + N);
+  std::vector<double2> tw64(N / 2);
+  for (int k = 0; k < N / 2; ++k) {
+    const double a = -2.0 * PI * (double)k / (double)N;
+    tw64[k] = make_double2(std::cos(a), std::sin(a));
+  }
   FbSchedule sch;
   build_schedule(cfg, K, woff, sch);
   p->n_passes = (int)sch.pass.size(); p->max_q = sch.max_q; p->b_pad = sch.b_pad; p->w_floats = (int)sch.w.size();
   p->fb_iters = sch.iters;
   if ((e = upload(&p->d_win, win)) != cudaSuccess || (e = upload(&p->d_tw1, tw1)) != cudaSuccess ||
+      (e = upload(&p->d_win64, win64)) != cudaSuccess || (e = upload(&p->d_tw64, tw64)) != cudaSuccess ||
       (e = upload(&p->d_tw2k, tw2k)) != cudaSuccess || (e = upload(&p->d_tw4k, tw4k)) != cudaSuccess ||
       (e = upload(&p->d_pass, sch.pass)) != cudaSuccess || (e = upload(&p->d_fbw, sch.w)) != cudaSuccess ||
       (e = upload(&p->d_fbstart, sch.start)) != cudaSuccess || (e = upload(&p->d_fbpid, sch.pid)) != cudaSuccess) {
@@ -340,7 +352,8 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
 
 extern "C" int mmb_plan_get_info(const mmb_plan* p, mmb_plan_info* info) {
   if (!p || !info) return fail(MMB_E_INVALID, "null argument");
-  info->frame_size = p->cfg.frame_size; info->num_bins = p->cfg.frame_size / 2; info->num_bands = p->cfg.num_bands;
+  info->frame_size = p->cfg.frame_size; info->num_bins = p->cfg.frame_size / 2 + (p->cfg.include_nyquist ? 1 : 0);
+  info->num_bands = p->cfg.num_bands;
   info->chunk_frames = p->chunk_frames; info->smem_bytes = p->smem_bytes; info->ctas_per_sm = 1;
   info->num_sms = p->num_sms; info->frames_per_round = mmb::frames_per_round(p->cfg.frame_size, p->group_warps);
   info->warps = p->warps;
@@ -433,16 +446,34 @@ static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
   return MMB_OK;
 }
 
+// Launches of one call: the raw-spectrum outputs (stft, spec) come from the float64 kernel (stft64.cu), everything
+// behind the filterbank and the lgd rows from the fused FP32 kernel.  *n_launched counts the kernels started.
 static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_prefix, int32_t n, int32_t chunks,
                   int chunk_frames, const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream,
-                  const mmb_outputs* extra = nullptr, int n_extra = 0, bool multicast = false) {
+                  int* n_launched, const mmb_outputs* extra = nullptr, int n_extra = 0, bool multicast = false) {
+  if (chunks < 1) return MMB_OK;
+  if (o->stft || o->spec) {
+    mmb::Stft64Params sp;
+    std::memset(&sp, 0, sizeof(sp));
+    sp.pcm = pcm_dev; sp.tracks = d_tracks; sp.chunk_prefix = d_prefix; sp.n_tracks = n; sp.chunk_frames = chunk_frames;
+    sp.hop = p->cfg.hop_size; sp.origin = p->cfg.origin; sp.circular_shift = p->cfg.circular_shift;
+    sp.include_nyquist = p->cfg.include_nyquist;
+    sp.spec_log_mode = p->cfg.num_bands == 0 ? p->cfg.log_mode : 0;
+    sp.mul = p->cfg.mul; sp.add = p->cfg.add;
+    sp.win = p->d_win64; sp.tw = p->d_tw64;
+    sp.out_stft = (float2*)o->stft; sp.ld_stft = o->ld_stft; sp.out_spec = o->spec; sp.ld_spec = o->ld_spec;
+    cudaError_t e = mmb::launch_stft64(p->cfg.frame_size, p->sample_bytes, sp, chunks, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "float64 STFT kernel launch");
+    if (n_launched) ++*n_launched;
+  }
+  const bool band_out = o->filt || o->log || o->diff || o->odf;
+  if (!band_out && !o->lgd) return MMB_OK;
   FrontendParams fp;
   std::memset(&fp, 0, sizeof(fp));
   fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunk_prefix = d_prefix; fp.n_tracks = n; fp.total_chunks = chunks;
   fp.chunk_frames = chunk_frames; fp.hop = p->cfg.hop_size; fp.origin = p->cfg.origin; fp.span_cap = p->span_cap;
   fp.win = p->d_win; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
-  const bool band_out = o->filt || o->log || o->diff || o->odf;
-  fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only stft/spec are wanted
+  fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only the lgd rows are wanted
   fp.n_passes = p->n_passes; fp.max_q = p->max_q; fp.b_pad = p->b_pad; fp.w_floats = p->w_floats;
   fp.fb_pass = p->d_pass; fp.fb_w = p->d_fbw; fp.fb_start = p->d_fbstart; fp.fb_pid = p->d_fbpid;
   fp.pcm_extent = pcm_extent; fp.bulk_allowed = ((uintptr_t)pcm_dev % 16) == 0;
@@ -450,8 +481,6 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.mul = p->cfg.mul; fp.add = p->cfg.add; fp.log_mode = p->cfg.log_mode;
   fp.diff_frames = p->cfg.diff_frames; fp.max_bins = p->cfg.diff_max_bins; fp.positive = p->cfg.positive_diffs;
   fp.circular_shift = p->cfg.circular_shift;
-  fp.spec_log_mode = p->cfg.num_bands == 0 ? p->cfg.log_mode : 0;
-  fp.out_stft = (float2*)o->stft; fp.ld_stft = o->ld_stft; fp.out_spec = o->spec; fp.ld_spec = o->ld_spec;
   fp.out_filt = o->filt; fp.ld_filt = o->ld_filt; fp.out_log = o->log; fp.ld_log = o->ld_log;
   fp.out_diff = o->diff; fp.ld_diff = o->ld_diff; fp.out_odf = o->odf;
   fp.out_lgd = o->lgd; fp.ld_lgd = o->ld_lgd;
@@ -460,9 +489,9 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   const int groups = p->warps / p->group_warps;
   int grid = p->num_sms;                              // one persistent CTA per SM
   if (grid > (chunks + groups - 1) / groups) grid = (chunks + groups - 1) / groups;
-  if (grid < 1) return MMB_OK;
   cudaError_t e = mmb::launch_frontend(p->cfg.frame_size, p->sample_bytes, fp, grid, p->smem_bytes, stream);
   if (e != cudaSuccess) return cuda_fail(e, "frontend kernel launch");
+  if (n_launched) ++*n_launched;
   return MMB_OK;
 }
 
@@ -473,8 +502,10 @@ extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_d
   int rc = check_outputs(p, outs);
   if (rc) return rc;
   CU(cudaSetDevice(p->cfg.device));
-  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, outs, (cudaStream_t)stream);
-  if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
+  int nl = 0;
+  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, outs,
+              (cudaStream_t)stream, &nl);
+  if (launches) *launches = nl;
   return rc;
 }
 
@@ -495,9 +526,10 @@ extern "C" int mmb_run_gather(const mmb_plan* p, const mmb_layout* l, const void
       return fail(MMB_E_INVALID, "every destination must hold the same outputs with the same leading dimensions");
   }
   CU(cudaSetDevice(p->cfg.device));
+  int nl = 0;
   rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, &dsts[0],
-              (cudaStream_t)stream, dsts + 1, n_dst - 1);
-  if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
+              (cudaStream_t)stream, &nl, dsts + 1, n_dst - 1);
+  if (launches) *launches = nl;
   return rc;
 }
 
@@ -510,9 +542,10 @@ extern "C" int mmb_run_multicast(const mmb_plan* p, const mmb_layout* l, const v
   if (mc->stft || mc->spec || mc->filt || mc->lgd)
     return fail(MMB_E_UNSUPPORTED, "mmb_run_multicast stores the band outputs log, diff and odf only");
   CU(cudaSetDevice(p->cfg.device));
+  int nl = 0;
   rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, mc,
-              (cudaStream_t)stream, nullptr, 0, true);
-  if (rc == MMB_OK && launches && l->total_chunks > 0) *launches = 1;
+              (cudaStream_t)stream, &nl, nullptr, 0, true);
+  if (launches) *launches = nl;
   return rc;
 }
 
@@ -549,7 +582,7 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
   for (int32_t i = 1; i < n; ++i)
     if (units[i].pcm_offset < units[i - 1].pcm_offset || units[i].out_row < units[i - 1].out_row + units[i - 1].frame_count)
       return fail(MMB_E_INVALID, "mmb_run_host needs units ordered by pcm_offset with consecutive, non-overlapping out_row ranges");
-  const int K = p->cfg.frame_size / 2, B = p->cfg.num_bands;
+  const int K = p->cfg.frame_size / 2 + (p->cfg.include_nyquist ? 1 : 0), B = p->cfg.num_bands;
   const size_t sb = (size_t)p->sample_bytes;
   // widths (elements) and element sizes of the six outputs: stft spec filt log diff odf
   void* hptr[7] = {oh->stft, oh->spec, oh->filt, oh->log, oh->diff, oh->odf, oh->lgd};
@@ -644,9 +677,8 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
       // synchronously by the runtime for pageable memory, so this is safe.
       if (prefix.back() > 0) {
         status = launch(p, S.d_tracks, S.d_prefix, (int32_t)tab.size(), prefix.back(), chunk_frames, S.d_pcm, pcm1 - pcm0, &od,
-                        S.stream);
+                        S.stream, &n_launch);
         if (status) goto done;
-        ++n_launch;
         for (int k = 0; k < 7; ++k) {
           if (!hptr[k]) continue;
           char* dst = (char*)hptr[k] + (size_t)row0 * hld[k] * esz[k];

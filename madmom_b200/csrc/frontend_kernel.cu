@@ -318,9 +318,9 @@ __device__ __forceinline__ void round_difference(const FrontendParams& p, const 
 }
 
 // ---------------------------------------------------------------------------------------------- the kernel
-// SPECOUT: per-bin outputs the launch may write: 0 none, 1 stft / spec, 2 lgd (N = 2048), 3 all of them.  Each
-// value is its own instantiation, so that e.g. launches that only produce band outputs are a
-// separate instantiation without the emitting copies of the splits.
+// SPECOUT: per-bin outputs the launch may write: 0 none, 2 lgd (N = 2048): its own instantiation, so that launches
+// that only produce band outputs carry no emitting copy of the split.  (Raw bins and magnitudes -- the `stft` and
+// `spec` outputs -- come from the float64 kernel in stft64.cu, not from here.)
 template <int N, typename S, bool GATHER, int SPECOUT>
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const FrontendParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -454,15 +454,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         const long long gA = D->g0 + fa, gB = gA + 1, ga = D->ga;
         const long long rowA = D->row0 + gA, rowB = rowA + 1;
         {
-          BinSink oa, ob;
-          oa.mag = my_mag; ob.mag = my_mag + 512; oa.sgn_odd = ob.sgn_odd = sgn_odd;
-          oa.log_mode = ob.log_mode = p.spec_log_mode; oa.mul = ob.mul = p.mul; oa.add = ob.add = p.add;
-          oa.stft_row = (p.out_stft && gA >= ga) ? p.out_stft + rowA * p.ld_stft : nullptr;
-          ob.stft_row = (p.out_stft && gB >= ga) ? p.out_stft + rowB * p.ld_stft : nullptr;
-          oa.spec_row = (p.out_spec && gA >= ga) ? p.out_spec + rowA * p.ld_spec : nullptr;
-          ob.spec_row = (p.out_spec && gB >= ga) ? p.out_spec + rowB * p.ld_spec : nullptr;
-          if ((SPECOUT & 1) && (oa.stft_row || oa.spec_row || ob.stft_row || ob.spec_row)) split_1024x2(lane, v, ex, oa, ob, haveB);
-          else split_1024x2(lane, v, ex, quiet(oa), quiet(ob), haveB);
+          BinSinkT<false> oa, ob;
+          oa.mag = my_mag; ob.mag = my_mag + 512;
+          split_1024x2(lane, v, ex, oa, ob, haveB);
         }
         if (nb > 0) {
           __syncwarp();
@@ -494,20 +488,14 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         core_pass2_fft(v);
         core_publish_upper(lane, v, ex, true);
         __syncwarp();
-        const long long g = D->g0 + gwarp, row = D->row0 + g;
-        const bool emit = g >= D->ga;
-        BinSink o;
-        o.mag = my_mag; o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
-        o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
-        o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
-        if ((SPECOUT & 2) && p.out_lgd && emit) {
-          if ((SPECOUT & 1) && (o.stft_row || o.spec_row))
-            split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
-          else split_2048_lgd(lane, v, ex, s_tw2k, quiet(o), p.out_lgd + row * p.ld_lgd, sgn_odd);
-        } else if ((SPECOUT & 1) && (o.stft_row || o.spec_row)) {
-          split_2048(lane, v, ex, s_tw2k, o);
+        BinSinkT<false> o;
+        o.mag = my_mag;
+        if (SPECOUT & 2) {
+          const long long g = D->g0 + gwarp, row = D->row0 + g;
+          if (p.out_lgd && g >= D->ga) split_2048_lgd(lane, v, ex, s_tw2k, o, p.out_lgd + row * p.ld_lgd, sgn_odd);
+          else split_2048(lane, v, ex, s_tw2k, o);
         } else {
-          split_2048(lane, v, ex, s_tw2k, quiet(o));
+          split_2048(lane, v, ex, s_tw2k, o);
         }
       } else {
 #pragma unroll 1
@@ -521,15 +509,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           core_pass2_fft(v);
           core_publish_upper(lane, v, ex, c == 0);
           __syncwarp();
-          const long long g = D->g0 + gwarp, row = D->row0 + g;
-          const bool emit = g >= D->ga;
-          BinSink o;
-          o.sgn_odd = sgn_odd; o.log_mode = p.spec_log_mode; o.mul = p.mul; o.add = p.add;
-          o.stft_row = (p.out_stft && emit) ? p.out_stft + row * p.ld_stft : nullptr;
-          o.spec_row = (p.out_spec && emit) ? p.out_spec + row * p.ld_spec : nullptr;
+          BinSinkT<false> o;
           o.mag = c == 0 ? my_mag_even : my_mag;
-          if ((SPECOUT & 1) && (o.stft_row || o.spec_row)) split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
-          else split_4096(lane, c, v, ex, s_tw2k, s_tw4k, quiet(o));
+          split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
           __syncwarp();
         }
       }
@@ -553,12 +535,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
 // ---------------------------------------------------------------------------------------------- host launchers
 template <int N, typename S>
 static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-  const bool bins = p.out_stft || p.out_spec, lgd = p.out_lgd != nullptr;
+  const bool lgd = p.out_lgd != nullptr;
   const int threads = p.warps * 32;
   if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true, 0><<<grid, threads, smem_bytes, stream>>>(p);
-  else if (N == 2048 && lgd && bins) frontend_kernel<N, S, false, (N == 2048 ? 3 : 1)><<<grid, threads, smem_bytes, stream>>>(p);
   else if (N == 2048 && lgd) frontend_kernel<N, S, false, (N == 2048 ? 2 : 0)><<<grid, threads, smem_bytes, stream>>>(p);
-  else if (bins) frontend_kernel<N, S, false, 1><<<grid, threads, smem_bytes, stream>>>(p);
   else frontend_kernel<N, S, false, 0><<<grid, threads, smem_bytes, stream>>>(p);
   return cudaGetLastError();
 }
@@ -595,9 +575,7 @@ template <int N, typename S>
 static cudaError_t set_one(int smem_bytes) {
   const cudaFuncAttribute a = cudaFuncAttributeMaxDynamicSharedMemorySize;
   cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false, 0>, a, smem_bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<N, S, false, 1>, a, smem_bytes);
   if (e == cudaSuccess && N == 2048) e = cudaFuncSetAttribute(frontend_kernel<N, S, false, (N == 2048 ? 2 : 0)>, a, smem_bytes);
-  if (e == cudaSuccess && N == 2048) e = cudaFuncSetAttribute(frontend_kernel<N, S, false, (N == 2048 ? 3 : 1)>, a, smem_bytes);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<N, S, true, 0>, a, smem_bytes);
   return e;
 }

@@ -158,8 +158,24 @@ inline SmemLayout smem_layout(int N, int warps, int group_warps, int n_bands, in
   return L;
 }
 
+// parameters of the float64 STFT kernel (stft64.cu): the launches that emit raw bins / magnitudes
+struct Stft64Params {
+  const void* pcm;
+  const Track* tracks;
+  const int32_t* chunk_prefix;
+  int32_t n_tracks, chunk_frames;
+  double hop;
+  int32_t origin, circular_shift, include_nyquist, spec_log_mode;
+  float mul, add;
+  const double* win;             // N doubles: fft_window as the reference multiplies it (float64, unscaled)
+  const double2* tw;             // N / 2 doubles2: W_N^k
+  float2* out_stft; int64_t ld_stft;
+  float* out_spec;  int64_t ld_spec;
+};
+
 cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, int grid, int smem_bytes,
                             cudaStream_t stream);
+cudaError_t launch_stft64(int N, int sample_bytes, const Stft64Params& p, int grid, cudaStream_t stream);
 cudaError_t frontend_set_smem(int N, int sample_bytes, int smem_bytes);
 // interleaved (num_frames, channels) int16 / float32 -> mono of the same type: mean over the channels with the
 // reference's rounding (np.mean(...).astype(dtype), signal.py:212), or one channel verbatim (channel >= 0)

@@ -1,0 +1,159 @@
+// Double-precision STFT for the launches that hand the raw spectrum to the caller (outputs `stft` / `spec`).
+//
+// The reference multiplies frame and window in float64, runs a float64 FFT and only then rounds the bins to
+// complex64 (madmom/audio/stft.py:105-131, :26); np.abs of those complex64 bins is the Spectrogram
+// (madmom/audio/spectrogram.py:122-141).  Consumers of the raw bins -- phase_deviation, rectified_complex_domain,
+// modified_kullback_leibler of an unfiltered spectrogram (madmom/features/onsets.py:320-581) -- take phases,
+// ratios and signs of bins that sit 70 dB below the loudest one, where an FP32 FFT is off by more than the bin
+// itself.  So this path computes like the reference: float64 products, float64 FFT, one rounding to float32 at
+// the store.  B200 runs FP64 at half the FP32 rate, and the path is bound by its 8 KB per frame of output
+// anyway.  The fused band-feature kernel (frontend_kernel.cu) stays FP32: its outputs pass a filterbank and a
+// logarithm and meet the tolerance with room to spare.
+//
+// One CTA per chunk of frames (same unit / chunk tables as the fused kernel); per frame: even/odd packing into an
+// M = N/2 point complex sequence in shared memory, radix-4 DIF passes (two radix-2 stages per pass, twiddles
+// W_N^k from a float64 table), a last radix-2 stage when log2 M is odd, real-FFT split straight out of the
+// bit-reversed positions.
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+#include "frontend_params.h"
+
+namespace mmb {
+
+namespace {
+
+__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ double2 cmuld(double2 a, double2 w) {
+  return make_double2(a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x);
+}
+
+template <int BITS>
+__device__ __forceinline__ int brev(int k) { return (int)(__brev((unsigned)k) >> (32 - BITS)); }
+
+__host__ __device__ constexpr int ilog2(int n) { return n <= 1 ? 0 : 1 + ilog2(n >> 1); }
+
+template <int N, typename S>
+__global__ void __launch_bounds__(256) stft64_kernel(const Stft64Params p) {
+  constexpr int M = N / 2, LOG_M = ilog2(M);
+  __shared__ double2 zs[M];
+  const int tid = threadIdx.x, nthreads = blockDim.x;
+  const int chunk = (int)blockIdx.x;
+  // unit of this chunk (binary search in the prefix sums, like next_round() of the fused kernel)
+  int lo = 0, hi = p.n_tracks;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (p.chunk_prefix[mid] <= chunk) lo = mid; else hi = mid;
+  }
+  const Track tr = p.tracks[lo];
+  const long long a_loc = (long long)(chunk - p.chunk_prefix[lo]) * p.chunk_frames;
+  const long long b_loc = min(a_loc + (long long)p.chunk_frames, (long long)tr.frame_count);
+  const S* src = reinterpret_cast<const S*>(p.pcm) + tr.pcm_offset;
+  const int out_bins = M + (p.include_nyquist ? 1 : 0);
+
+  for (long long f = a_loc; f < b_loc; ++f) {
+    const long long g = tr.frame_first + f;
+    // int(index * hop_size) - frame_size // 2 - origin in float64, truncation (signal.py:917-919)
+    const long long s0 = __double2ll_rz((double)g * p.hop) - (long long)(N / 2) - (long long)p.origin - tr.sample_base;
+    // ---- frame * fft_window in float64; circular shift swaps the halves (stft.py:106-124)
+    for (int n = tid; n < M; n += nthreads) {
+      double v[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int j = 2 * n + h;                              // position in the FFT input
+        const int i = p.circular_shift ? (j + N / 2) & (N - 1) : j;      // sample of the frame that sits there
+        const long long li = s0 + i;
+        double x = 0.0;
+        if (li >= 0 && li < tr.pcm_len) x = (double)src[li];
+        v[h] = x * p.win[i];
+      }
+      zs[n] = make_double2(v[0], v[1]);
+    }
+    __syncthreads();
+    // ---- radix-4 DIF passes: stages with half-sizes h and h / 2 on the points i, i + h/2, i + h, i + 3h/2
+    int h = M / 2;
+    for (; h >= 2; h >>= 2) {
+      const int q2 = h >> 1;                                   // half-size of the second stage
+      for (int q = tid; q < M / 4; q += nthreads) {
+        const int pidx = q & (q2 - 1);
+        const int i0 = ((q / q2) * 2 * h) + pidx;
+        double2 a0 = zs[i0], a1 = zs[i0 + q2], a2 = zs[i0 + h], a3 = zs[i0 + h + q2];
+        // first stage: (a0, a2) twiddle W_{2h}^pidx, (a1, a3) twiddle W_{2h}^(pidx + h/2); W_{2h}^m = W_N^(m N / 2h)
+        const int s1 = N / (2 * h);
+        const double2 w0 = p.tw[pidx * s1], w1 = p.tw[(pidx + q2) * s1];
+        double2 b0 = cadd(a0, a2), b2 = cmuld(csub(a0, a2), w0);
+        double2 b1 = cadd(a1, a3), b3 = cmuld(csub(a1, a3), w1);
+        // second stage (half-size h/2): (b0, b1) and (b2, b3), twiddle W_h^pidx = W_N^(pidx N / h)
+        const double2 w2 = p.tw[pidx * (N / h)];
+        zs[i0] = cadd(b0, b1);
+        zs[i0 + q2] = cmuld(csub(b0, b1), w2);
+        zs[i0 + h] = cadd(b2, b3);
+        zs[i0 + h + q2] = cmuld(csub(b2, b3), w2);
+      }
+      __syncthreads();
+    }
+    if (h == 1) {                                             // log2 M odd: one radix-2 stage is left (no twiddle)
+      for (int q = tid; q < M / 2; q += nthreads) {
+        const double2 a0 = zs[2 * q], a1 = zs[2 * q + 1];
+        zs[2 * q] = cadd(a0, a1);
+        zs[2 * q + 1] = csub(a0, a1);
+      }
+      __syncthreads();
+    }
+    // ---- real-FFT split, Z[k] sits at the bit-reversed position:
+    //      X[k] = (Z[k] + conj Z[M-k]) / 2 + W_N^k (Z[k] - conj Z[M-k]) / 2i
+    const long long row = tr.out_row + f;
+    for (int k = tid; k < out_bins; k += nthreads) {
+      double re, im;
+      if (k == M) {
+        const double2 z0 = zs[0];
+        re = z0.x - z0.y; im = 0.0;
+      } else {
+        const double2 zk = zs[brev<LOG_M>(k)];
+        const double2 zm = zs[brev<LOG_M>((M - k) & (M - 1))];
+        const double ar = 0.5 * (zk.x + zm.x), ai = 0.5 * (zk.y - zm.y);
+        const double br = 0.5 * (zk.y + zm.y), bi = -0.5 * (zk.x - zm.x);
+        const double2 w = p.tw[k];
+        re = ar + (br * w.x - bi * w.y);
+        im = ai + (br * w.y + bi * w.x);
+      }
+      const float rf = (float)re, imf = (float)im;            // the reference's complex64 store
+      if (p.out_stft) p.out_stft[row * p.ld_stft + k] = make_float2(rf, imf);
+      if (p.out_spec) {
+        // np.abs of the complex64 bin, float32 (spectrogram.py:22-38)
+        float m = (float)sqrt((double)rf * (double)rf + (double)imf * (double)imf);
+        if (p.spec_log_mode != 0) {                           // LogarithmicSpectrogram of an unfiltered one (:527-534)
+          const float y = __fadd_rn(__fmul_rn(m, p.mul), p.add);
+          m = p.spec_log_mode == 1 ? (float)log10((double)y) : p.spec_log_mode == 3 ? (float)log((double)y)
+            : p.spec_log_mode == 4 ? (float)log2((double)y) : y;
+        }
+        p.out_spec[row * p.ld_spec + k] = m;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+template <int N, typename S>
+cudaError_t launch_n(const Stft64Params& p, int grid, cudaStream_t stream) {
+  stft64_kernel<N, S><<<grid, 256, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_stft64(int N, int sample_bytes, const Stft64Params& p, int grid, cudaStream_t stream) {
+  if (sample_bytes == 2) {
+    if (N == 1024) return launch_n<1024, int16_t>(p, grid, stream);
+    if (N == 2048) return launch_n<2048, int16_t>(p, grid, stream);
+    if (N == 4096) return launch_n<4096, int16_t>(p, grid, stream);
+  } else if (sample_bytes == 4) {
+    if (N == 1024) return launch_n<1024, float>(p, grid, stream);
+    if (N == 2048) return launch_n<2048, float>(p, grid, stream);
+    if (N == 4096) return launch_n<4096, float>(p, grid, stream);
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace mmb

@@ -46,6 +46,11 @@ def ref_synth():
 
 
 @pytest.fixture(scope="session")
+def ref_mel():
+    return _npz("ref_mel.npz")
+
+
+@pytest.fixture(scope="session")
 def ref_odfs():
     return _npz("ref_odfs.npz")
 

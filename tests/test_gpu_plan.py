@@ -46,11 +46,23 @@ def _run_all(plan, tracks, hop):
     return {k: v.cpu().numpy() for k, v in outs.items()}, T
 
 
+def assert_bins_close(got, ref, what=""):
+    """Raw bins / magnitudes: the reference rounds a float64 FFT once to complex64 (stft.py:26, :105-131) and so does
+    the float64 kernel (csrc/stft64.cu): per component at most one float32 ulp (rounding of two float64 results that
+    differ in their last bits) plus 1e-10 of the largest bin."""
+    got, ref = np.asarray(got), np.asarray(ref)
+    assert got.shape == ref.shape, (what, got.shape, ref.shape)
+    scale = float(np.abs(ref).max()) if ref.size else 0.0
+    parts = [(got.real, ref.real), (got.imag, ref.imag)] if np.iscomplexobj(ref) else [(got, ref)]
+    for a, b in parts:
+        err = np.abs(a.astype(np.float64) - b.astype(np.float64))
+        bound = 3e-7 * np.abs(b.astype(np.float64)) + 1e-10 * scale
+        assert (err <= bound).all(), "%s: worst excess %g (scale %g)" % (what, float((err - bound).max()), scale)
+
+
 def _check_stages(got, ref, what):
-    scale = np.abs(ref["stft"]).max()
-    # complex STFT: the reference rounds a float64 FFT to complex64; an FP32 FFT differs by ~1e-7 * max|X|
-    assert np.abs(got["stft"] - ref["stft"]).max() <= 2e-6 * scale, what
-    assert np.abs(got["spec"] - ref["spec"]).max() <= 2e-6 * scale, what
+    assert_bins_close(got["stft"], ref["stft"], what + " stft")
+    assert_bins_close(got["spec"], ref["spec"], what + " spec")
     assert_close(got["filt"], ref["filt"], what=what + " filt")
     assert_close(got["log"], ref["log"], what=what + " log")
     assert_close(got["diff"], ref["diff"], what=what + " diff")
@@ -81,8 +93,8 @@ def test_superflux_golden(sample_pcm, ref_sample):
     assert np.allclose(got["spec"][0, :8], [3.15249, 4.00272, 5.66156, 6.30141, 6.02199, 10.84909, 17.83130,
                                             19.44511])
     rows = ref_sample["rows"]
-    scale = np.abs(ref_sample["stft_rows"]).max()
-    assert np.abs(got["stft"][rows] - ref_sample["stft_rows"]).max() <= 2e-6 * scale
+    assert_bins_close(got["stft"][rows], ref_sample["stft_rows"], "stft rows vs reference")
+    assert_bins_close(got["spec"][rows], ref_sample["spec_rows"], "spec rows vs reference")
 
 
 def test_fps200_fractional_hop_and_peaks(sample_pcm, ref_sample):
@@ -106,8 +118,31 @@ def test_circular_shift_stft(sample_pcm, ref_sample):
     plan, _ = _plan_for(np.int16, 2048, 441., 24, False, circ=True)
     got, _ = _run_all(plan, [sample_pcm], 441.)
     rows = ref_sample["rows"]
-    scale = np.abs(ref_sample["stft_circ_rows"]).max()
-    assert np.abs(got["stft"][rows] - ref_sample["stft_circ_rows"]).max() <= 2e-6 * scale
+    assert_bins_close(got["stft"][rows], ref_sample["stft_circ_rows"], "circular shift vs reference")
+
+
+@pytest.mark.parametrize("N", [1024, 2048, 4096])
+def test_include_nyquist(sample_pcm, N):
+    """include_nyquist (stft.py:93-95): frame_size / 2 + 1 bins for the stft / spec outputs, float32 PCM and a
+    circular shift included; a plan with a filterbank refuses it."""
+    from oracle import frontend as O
+    from madmom_b200 import _lib
+    x = (sample_pcm[:30000].astype(np.float64) / 32767.).astype(np.float32) if N == 1024 else sample_pcm[:30000]
+    circ = N == 4096
+    fw = O.fft_window(np.hanning(N), N, x.dtype)
+    plan = _lib.FrontEndPlan(N, 441., fw, pcm_dtype=x.dtype, circular_shift=circ, include_nyquist=True)
+    assert plan.num_bins == N // 2 + 1
+    T = _lib.num_frames(len(x), 441.)
+    outs = {"stft": torch.empty((T, N // 2 + 1), dtype=torch.complex64, device="cuda"),
+            "spec": torch.empty((T, N // 2 + 1), device="cuda")}
+    assert plan.run(torch.from_numpy(x).cuda(), _lib.make_units([len(x)], [T]), outs) == 1
+    ref = O.stft(O.framed(x, N, 441.), fw, circular_shift=circ, include_nyquist=True)
+    assert ref.shape == (T, N // 2 + 1)
+    assert_bins_close(outs["stft"].cpu().numpy(), ref, "include_nyquist stft N=%d" % N)
+    assert_bins_close(outs["spec"].cpu().numpy(), O.spec(ref), "include_nyquist spec N=%d" % N)
+    with pytest.raises(NotImplementedError):
+        _lib.FrontEndPlan(N, 441., fw, pcm_dtype=x.dtype, include_nyquist=True,
+                          filterbank=O.logarithmic_filterbank(O.fft_frequencies(N // 2, 44100), 12))
 
 
 @pytest.mark.parametrize("N,bpo,norm,mul,ratio", [(2048, 12, False, 1., .5), (1024, 6, True, 5., .25),

@@ -201,26 +201,68 @@ def test_frame_slices_and_origins(sig, sample_pcm):
         assert np.abs(got - ref).max() <= 2e-6 * np.abs(ref).max()
 
 
-def test_float_signal_window_none_and_mel(sample_pcm):
+def test_float_signal_window_none(sample_pcm):
     from oracle import frontend as O
-    from madmom_b200.audio.filters import MelFilterbank
     from madmom_b200.audio.signal import Signal, FramedSignal
     from madmom_b200.audio.stft import ShortTimeFourierTransform
-    from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
+    from madmom_b200.audio.spectrogram import Spectrogram
     x = (sample_pcm.astype(np.float64) / 32767.).astype(np.float32)
     frames = FramedSignal(Signal(x, sample_rate=44100), frame_size=1024, hop_size=441.)
     got = np.asarray(Spectrogram(ShortTimeFourierTransform(frames, window=None)))
     ref = O.spec(O.stft(O.framed(x, 1024, 441.), None))
     assert np.abs(got - ref).max() <= 2e-6 * np.abs(ref).max()
-    # Mel filterbank with duplicate low bands + natural log (CNNOnsetProcessor front end, onsets.py:838-871)
-    lf = LogarithmicFilteredSpectrogram(frames, filterbank=MelFilterbank, num_bands=80, fmin=27.5, fmax=16000,
-                                        norm_filters=True, unique_filters=False, log=np.log, add=2.220446049250313e-16)
-    S = O.spec(O.stft(O.framed(x, 1024, 441.), O.fft_window(np.hanning, 1024, np.float32)))
-    want = O.logarithmic(O.filtered(S, np.asarray(lf.filterbank)), 1., np.float32(2.220446049250313e-16), np.log)
-    assert lf.shape == want.shape == (281, 80)
-    # log(x + eps) of tiny band energies amplifies relative FFT rounding: compare where the band is not ~0
-    big = O.filtered(S, np.asarray(lf.filterbank)) > 1e-6
-    assert_close(np.asarray(lf)[big], want[big], rtol=1e-4, atol=2e-5, what="mel ln")
+
+
+def test_mel_filterbank_and_cnn_front_end(sig, ref_mel):
+    """SURVEY 8(f) row 2 against vectors of the real reference (tests/golden/make_golden_mel.py):
+    FilteredSpectrogram(MelFilterbank, 40) with the literals of tests/test_audio_spectrogram.py:173-180, a
+    rectangular (Bark) bank as a non-triangular case, and the CNNOnsetProcessor front end spelled as the reference
+    does (features/onsets.py:838-871): Mel 80 bands 27.5 Hz .. 16 kHz with duplicate low bands, ln(x + EPSILON),
+    np.dstack over frame sizes [2048, 1024, 4096].  Standard bound, no mask."""
+    from madmom_b200.processors import ParallelProcessor, SequentialProcessor
+    from madmom_b200.audio.filters import Filterbank, MelFilterbank
+    from madmom_b200.audio.signal import FramedSignalProcessor, SignalProcessor
+    from madmom_b200.audio.stft import ShortTimeFourierTransformProcessor
+    from madmom_b200.audio.spectrogram import (FilteredSpectrogram, FilteredSpectrogramProcessor,
+                                               LogarithmicSpectrogramProcessor)
+    from madmom_b200.recipe import fft_frequencies
+    mel = FilteredSpectrogram(sig, filterbank=MelFilterbank, num_bands=40)
+    assert mel.shape == (281, 40)
+    assert np.allclose(mel[0, :6], [8.42887115, 17.98174477, 19.50165367, 6.48194313, 2.96991181, 4.06280804])
+    assert_close(np.asarray(mel), ref_mel["filt_mel40"], what="FilteredSpectrogram(MelFilterbank)")
+    bark = Filterbank(ref_mel["bark_N2048_dense"], fft_frequencies(1024, 44100))
+    got = FilteredSpectrogram(sig, filterbank=bark)
+    assert np.allclose(got[0, :6], [16.42251968, 17.36715126, 2.81979132, 4.27050114, 3.08699131, 1.50553513])
+    assert_close(np.asarray(got), ref_mel["filt_bark"], what="FilteredSpectrogram(rectangular bank)")
+    EPSILON = np.spacing(1)
+    multi = ParallelProcessor([])
+    for frame_size in [2048, 1024, 4096]:
+        frames = FramedSignalProcessor(frame_size=frame_size, fps=100)
+        stft = ShortTimeFourierTransformProcessor()
+        filt = FilteredSpectrogramProcessor(filterbank=MelFilterbank, num_bands=80, fmin=27.5, fmax=16000,
+                                            norm_filters=True, unique_filters=False)
+        spec = LogarithmicSpectrogramProcessor(log=np.log, add=EPSILON)
+        multi.append(SequentialProcessor((frames, stft, filt, spec)))
+    pre = SequentialProcessor((SignalProcessor(num_channels=1, sample_rate=44100), multi, np.dstack))
+    out = pre(sig)
+    assert out.shape == (281, 80, 3) and out.dtype == np.float32
+    assert_close(out, ref_mel["cnn_onset_frontend"], what="CNN onset front end")
+
+
+def test_spectrogram_of_a_spectrogram_keeps_the_data(sig, ref_sample):
+    """Spectrogram(x) / SpectrogramProcessor()(x) for x already a (filtered / logarithmic) Spectrogram keeps x's
+    matrix and only re-types it (madmom/audio/spectrogram.py:125-127)."""
+    from madmom_b200.audio.spectrogram import (Spectrogram, SpectrogramProcessor, LogarithmicFilteredSpectrogram,
+                                               FilteredSpectrogram, LogarithmicSpectrogram)
+    lfs = LogarithmicFilteredSpectrogram(sig)
+    again = SpectrogramProcessor()(lfs)
+    assert type(again) is Spectrogram and again.shape == (281, 81) and again.num_bins == 81
+    assert_close(np.asarray(again), ref_sample["logfilt12n"], what="Spectrogram(LogarithmicFilteredSpectrogram)")
+    assert again.stft is lfs.stft
+    with pytest.raises(NotImplementedError):
+        FilteredSpectrogram(again)                     # no second filterbank on the GPU path
+    with pytest.raises(NotImplementedError):
+        LogarithmicSpectrogram(again)
 
 
 def test_errors(sig):
@@ -373,8 +415,9 @@ def test_complex_flux(sig, ref_sample):
 def test_other_spectral_odfs(sample_pcm, ref_odfs, which):
     """the remaining onset detection functions of madmom/features/onsets.py, with the inputs the
     reference's tests use (tests/test_features_onsets.py:24-27), against vectors computed by the real reference.
-    The phase-based functions average over all 1024 bins, noise bins included, whose phases carry the rounding of
-    the FP32 FFT (the reference's is float64): their bound is printed and asserted separately."""
+    The phase-based functions average over all 1024 bins, noise-floor bins included, so they need the raw bins as the
+    reference has them: the stft / spec matrices come from the float64 kernel (csrc/stft64.cu), and every function
+    meets the standard bound 1e-5 + 1e-4 |ref| on both inputs."""
     from madmom_b200.audio.signal import Signal
     from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
     from madmom_b200.features import onsets as ON
@@ -395,7 +438,7 @@ def test_other_spectral_odfs(sample_pcm, ref_odfs, which):
         assert a.shape == want.shape, k
         worst[k] = float(np.max(np.abs(a - want) / (1e-5 + 1e-4 * np.abs(want))))
     print(which, {k: round(v, 3) for k, v in worst.items()})
-    for k in ("hfc_logfilt", "hfc_spec", "sd_logfilt", "sd_spec", "mkl_logfilt", "wpd", "nwpd", "cd"):
+    for k in worst:
         assert worst[k] <= 1.0, (k, worst[k])
     if which == "sample":
         # reference literals, tests/test_features_onsets.py:35-152
@@ -405,8 +448,6 @@ def test_other_spectral_odfs(sample_pcm, ref_odfs, which):
                                                       196.88954163, 200.32469177], rtol=1e-4)
         assert np.allclose(np.asarray(got["wpd"])[:6], [0, 0, 0.19568817, 0.20483065, 0.17890805, 0.16970603],
                            rtol=1e-4)
-    # phase of noise-floor bins / ratio of noise-floor magnitudes / sign of tiny magnitude changes
-    assert worst["pd"] <= 50.0 and worst["mkl_spec"] <= 50.0 and worst["rcd"] <= 50.0, worst
 
 
 def test_spectral_odf_errors(sig):

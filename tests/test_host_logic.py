@@ -96,6 +96,52 @@ def test_product_filterbank_misc(ref_filterbanks):
         F.Filterbank(np.zeros((10, 2)), np.arange(9))
 
 
+def test_mel_filterbank_bit_exact(ref_mel):
+    """SURVEY 8(f) row 2: MelFilterbank against tables computed by the real reference (filters.py:1035-1092;
+    tests/test_audio_filters.py:845-905): the 40-band default and the CNNOnsetProcessor bank (80 bands, 27.5 Hz ..
+    16 kHz, normalised, duplicate low bands kept) for all three frame sizes, weights bit for bit."""
+    from madmom_b200.audio.filters import MelFilterbank
+    from madmom_b200.recipe import fft_frequencies
+    fb = MelFilterbank(fft_frequencies(1024, 44100))
+    s, l, w = fb.band_table()
+    assert fb.shape == (1024, 40)
+    assert np.array_equal(s, ref_mel["mel40_N2048_start"]) and np.array_equal(l, ref_mel["mel40_N2048_len"])
+    assert np.array_equal(w, ref_mel["mel40_N2048_w"])
+    assert np.array_equal(fb.center_frequencies, ref_mel["mel40_N2048_center"])
+    for N in (1024, 2048, 4096):
+        fb = MelFilterbank(fft_frequencies(N // 2, 44100), num_bands=80, fmin=27.5, fmax=16000, norm_filters=True,
+                           unique_filters=False)
+        assert fb.shape == (N // 2, 80) and fb.dtype == np.float32
+        assert np.array_equal(np.asarray(fb), ref_mel["mel80_N%d_dense" % N])
+        assert np.array_equal(fb.center_frequencies, ref_mel["mel80_N%d_center" % N])
+
+
+def test_gain_attenuate_normalize(ref_mel):
+    """adjust_gain / attenuate / normalize (madmom/audio/signal.py:71-167) against the real
+    reference's outputs, through the functions and through Signal(norm=..., gain=...)."""
+    from madmom_b200.audio import signal as S
+    x16, xf = ref_mel["ingest_i16"], ref_mel["ingest_f32"]
+    for tag, x in (("i16", x16), ("f32", xf)):
+        for gain in (-6.5, 0.0, 3.0):
+            key = "gain_%s_%g" % (tag, gain)
+            if key not in ref_mel:
+                with pytest.raises(ValueError):
+                    S.adjust_gain(x, gain)
+                continue
+            got = S.adjust_gain(x, gain)
+            assert got.dtype == x.dtype and np.array_equal(got, ref_mel[key])
+        assert np.array_equal(S.attenuate(x, 10.), ref_mel["atten_%s_10" % tag])
+        assert S.attenuate(x, 0) is x
+    assert np.array_equal(S.normalize(xf), ref_mel["norm_f32"]) and np.array_equal(S.normalize(x16), ref_mel["norm_i16"])
+    with pytest.raises(ValueError):
+        S.normalize(x16.astype(np.int8))
+    sig = S.Signal(x16, sample_rate=44100, norm=True, gain=-6.5)
+    assert isinstance(sig, S.Signal) and sig.dtype == np.int16 and sig.sample_rate == 44100
+    assert np.array_equal(np.asarray(sig), S.adjust_gain(S.normalize(x16), -6.5))
+    proc = S.SignalProcessor(sample_rate=44100, gain=-6.5)
+    assert np.array_equal(np.asarray(proc(xf)), ref_mel["gain_f32_-6.5"])
+
+
 def test_signal_and_framed_signal(sample_pcm, ref_sample):
     from madmom_b200.audio.signal import Signal, FramedSignal, FramedSignalProcessor
     sig = Signal(sample_pcm, sample_rate=44100)

@@ -230,6 +230,11 @@ MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops);
  * per second over the whole device. */
 MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s);
 
+/* Ceiling of the fused kernel: frames per second of its warp-level real FFT alone (frame_size 2048: both 32-point
+ * register passes, the shared-memory transpose, inter-pass twiddles, real-FFT split and magnitudes, 16 warps per SM;
+ * no PCM staging, window, filterbank, difference or stores).  bench.py reports the fused kernel against it. */
+MMB_API int mmb_fft_probe(int32_t device, int32_t frame_size, double* frames_per_s);
+
 #ifdef __cplusplus
 }
 #endif

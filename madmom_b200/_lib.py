@@ -66,6 +66,7 @@ EXPORTS = {
     "mmb_host_free": (c_i32, [c_vp]),
     "mmb_measure_fp32_peak": (c_i32, [c_i32, ctypes.POINTER(c_f64)]),
     "mmb_rate_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
+    "mmb_fft_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
     "mmb_matrix_diff": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i32, c_i64, c_i32, c_i32, c_i32, c_vp]),
     "mmb_complex_flux": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_i32, c_i32, c_i64, c_i64, c_vp, c_i32, c_i32,
                                  c_vp, c_vp]),
@@ -133,6 +134,13 @@ def measure_fp32_peak(device=0):
     return v.value
 
 
+def fft_only_frames_per_s(device=0, frame_size=2048):
+    """Frames per second of the fused kernel's warp FFT alone (mmb_fft_probe): the ceiling it is judged against."""
+    v = c_f64(0.0)
+    _check(load().mmb_fft_probe(int(device), int(frame_size), ctypes.byref(v)))
+    return v.value
+
+
 def compact_filterbank(fb):
     """(K, B) dense float32 filterbank -> (start[B], len[B], weights[nnz]): one run min..max nonzero per band."""
     fb = np.asarray(fb, dtype=np.float32)
@@ -176,6 +184,7 @@ class FrontEndPlan(object):
         self._lib = lib
         self._handle = c_vp()
         self._layouts = {}
+        self._layout_lock = threading.Lock()
         self.frame_size, self.hop_size, self.origin = int(frame_size), float(hop_size), int(origin)
         self.num_bins = self.frame_size // 2 + (1 if include_nyquist else 0)
         self.device = int(device)
@@ -226,17 +235,34 @@ class FrontEndPlan(object):
         return {"stft": self.num_bins, "spec": self.num_bins, "lgd": self.num_bins, "odf": 1}.get(name, self.num_bands)
 
     def _layout(self, units):
+        """Device copy of a unit table, cached by content (least recently used of 64 kept).  Destroying a layout
+        frees device memory, which waits for the kernels that read it, so an evicted layout is never pulled from
+        under a launch already enqueued; the lock keeps two host threads from evicting under each other."""
         key = units.tobytes()
-        h = self._layouts.get(key)
-        if h is None:
-            if len(self._layouts) > 16:
-                for old in self._layouts.values():
+        with self._layout_lock:
+            h = self._layouts.pop(key, None)
+            if h is None:
+                while len(self._layouts) >= 64:
+                    old = self._layouts.pop(next(iter(self._layouts)))
                     self._lib.mmb_layout_destroy(old)
-                self._layouts.clear()
-            h = c_vp()
-            _check(self._lib.mmb_layout_create(self._handle, units.ctypes.data_as(c_vp), len(units), ctypes.byref(h)))
-            self._layouts[key] = h
+                h = c_vp()
+                _check(self._lib.mmb_layout_create(self._handle, units.ctypes.data_as(c_vp), len(units),
+                                                   ctypes.byref(h)))
+            self._layouts[key] = h                       # (re-)inserted last: most recently used
         return h
+
+    @staticmethod
+    def _check_extents(units, pcm_elems, out_rows):
+        """The unit table must stay inside the tensors handed in: the kernel trusts it."""
+        if len(units) == 0:
+            return
+        need_pcm = int((units["pcm_offset"] + units["pcm_len"]).max())
+        if need_pcm > pcm_elems:
+            raise ValueError("unit table reads %d PCM samples, the pcm tensor has %d" % (need_pcm, pcm_elems))
+        need_rows = int((units["out_row"] + units["frame_count"]).max())
+        for name, rows in out_rows.items():
+            if rows < need_rows:
+                raise ValueError("output %r has %d rows, the unit table writes %d" % (name, rows, need_rows))
 
     @staticmethod
     def _fill(outs, ptrs):
@@ -273,7 +299,10 @@ class FrontEndPlan(object):
             else:
                 if t.dim() != 2 or t.stride(1) != 1 or t.shape[1] != self.width(name):
                     raise ValueError("output %s must be (rows, %d) with unit column stride" % (name, self.width(name)))
+                if t.stride(0) < self.width(name) and t.shape[0] > 1:
+                    raise ValueError("output %s: row stride smaller than the row width" % name)
                 ptrs[name] = (t.data_ptr(), t.stride(0))
+        self._check_extents(units, pcm.numel(), {name: t.shape[0] for name, t in outputs.items()})
         o = self._fill(outputs, ptrs)
         if stream is None:
             stream = torch.cuda.current_stream(self.device).cuda_stream

@@ -151,6 +151,70 @@ class BatchFrontEnd(object):
         return out
 
 
+    # ------------------------------------------------------------------------------------------ program
+    def onsets_host(self, pcm, lengths, threshold, fps=None, smooth=0., pre_avg=0., post_avg=0., pre_max=0.,
+                    post_max=0., group_tracks=128):
+        """The whole onset program for a batch of tracks held in host memory (bin/LogFiltSpecFlux, bin/SuperFlux:
+        SpectralOnsetProcessor -> OnsetPeakPickingProcessor.process, madmom/features/onsets.py:651-684, 1076-1107,
+        without the final combine_events): PCM in, peak frame indices out.  Groups of tracks are copied to the device
+        on alternating streams while the fused kernel works on the previous group; only the onset detection
+        function stays on the device, peaks are picked there (mmb_peak_picking, one segment per track) and only
+        the peak indices and per-track counts travel back.  Returns (peaks int32 [total], counts int32 [tracks],
+        seg_offsets int64 [tracks + 1]): track i's peaks are peaks[seg[i] : seg[i] + counts[i]] (frame indices)."""
+        import torch
+        if len(self.plans) != 1:
+            raise ValueError("onsets_host needs a single recipe")
+        plan = self.plans[0]
+        if isinstance(pcm, np.ndarray):
+            pcm = torch.from_numpy(pcm)
+        if pcm.dim() == 2 and lengths is None:
+            lengths = [pcm.shape[1]] * pcm.shape[0]
+        pcm = pcm.reshape(-1)
+        fps = self.recipes[0].fps if fps is None else fps
+        T = self.frame_counts(lengths)
+        n = len(T)
+        offs = np.concatenate(([0], np.cumsum(lengths))).astype(np.int64)
+        seg = np.concatenate(([0], np.cumsum(T))).astype(np.int64)
+        dev = torch.device("cuda", self.device)
+        st = getattr(self, "_prog_state", None)
+        max_group = max(int(offs[min(i + group_tracks, n)] - offs[i]) for i in range(0, n, group_tracks))
+        if st is None or st["cap"] < max_group or st["rows"] < int(seg[-1]):
+            st = {"cap": max_group, "rows": int(seg[-1]),
+                  "slots": [torch.empty((max_group,), dtype=pcm.dtype, device=dev) for _ in range(3)],
+                  "streams": [torch.cuda.Stream(device=dev) for _ in range(3)],
+                  "odf": torch.empty((int(seg[-1]),), dtype=torch.float32, device=dev)}
+            self._prog_state = st
+        odf = st["odf"][:int(seg[-1])]
+        cur = torch.cuda.current_stream(dev)
+        for s in st["streams"]:
+            s.wait_stream(cur)
+        for g, i0 in enumerate(range(0, n, group_tracks)):
+            i1 = min(i0 + group_tracks, n)
+            stream, slot = st["streams"][g % 3], st["slots"][g % 3]
+            a, b = int(offs[i0]), int(offs[i1])
+            with torch.cuda.stream(stream):
+                slot[:b - a].copy_(pcm[a:b], non_blocking=True)
+                units = _lib.make_units(lengths[i0:i1], T[i0:i1])
+                plan.run(slot, units, {"odf": odf[int(seg[i0]):int(seg[i1])]}, stream=stream.cuda_stream)
+        for s in st["streams"]:
+            cur.wait_stream(s)
+        frames = np.round(np.array([smooth, pre_avg, post_avg, pre_max, post_max]) * fps).astype(int)
+        peaks, counts = _lib.peak_picking(odf, threshold, int(frames[0]), int(frames[1]), int(frames[2]),
+                                          int(frames[3]), int(frames[4]), torch.from_numpy(seg).to(dev))
+        counts_h = counts.cpu()
+        # ascending indices per segment sit at the start of the segment's range: gather the used prefixes on the device
+        total = int(counts_h.sum())
+        if total:
+            segd = torch.from_numpy(seg[:-1]).to(dev)
+            starts = torch.repeat_interleave(segd, counts.long())
+            within = torch.arange(total, device=dev) - torch.repeat_interleave(
+                torch.cumsum(counts.long(), 0) - counts.long(), counts.long())
+            packed = peaks[starts + within].cpu()
+        else:
+            packed = torch.empty((0,), dtype=torch.int32)
+        return packed, counts_h, seg
+
+
 def complex_flux_batch(fe, pcm, lengths, temporal_filter=3, scratch_bytes=None):
     """ComplexFlux ODF (config 5 of BASELINE.json) for a batch of tracks on the device.  The per-bin local group
     delay matrix is an intermediate of rows x K floats, so the batch is walked in groups of tracks whose scratch

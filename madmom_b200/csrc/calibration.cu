@@ -2,7 +2,10 @@
 // front end) measured the same way MEASURED_PEAKS.json measures HBM and bf16: a
 // dependent-chain FFMA kernel over all SMs, best of several launches, CUDA events.
 #include <cuda_runtime.h>
+#include <cmath>
+#include <vector>
 #include "../../include/madmom_b200.h"
+#include "frame_fft.cuh"
 
 namespace {
 template <int ILP>
@@ -140,4 +143,99 @@ extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* gin
   cudaFree(d);
   *ginst_per_s = best;
   return MMB_OK;
+}
+
+// ---- FFT-only ceiling of the fused kernel --------------------------------------------------------------
+// The same warp-level 2048-point real FFT the front end runs per frame (core_pass1 / core_pass2 / publish / split
+// with magnitudes into the warp's scratch), 16 warps per SM, inputs made up in registers: no PCM staging, no
+// window, no filterbank, no difference, no global stores.  Its frame rate is the ceiling the fused kernel is
+// judged against (bench.py: roofline.fft_only).
+namespace {
+__global__ void __launch_bounds__(512, 1) fft_only_kernel(const float2* __restrict__ tw1, const float2* __restrict__ tw2k,
+                                                           int iters, float* out) {
+  using namespace mmb;
+  extern __shared__ __align__(16) unsigned char smem[];
+  float2* s_tw1 = reinterpret_cast<float2*>(smem);
+  float2* s_tw2k = reinterpret_cast<float2*>(smem + 8192);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned char* my = smem + 8192 + 4096 + warp * (8448 + 16);
+  float2* ex = reinterpret_cast<float2*>(my);
+  float* mag = reinterpret_cast<float*>(my);
+  for (int i = tid; i < 1024; i += blockDim.x) s_tw1[i] = tw1[i];
+  for (int i = tid; i < 512; i += blockDim.x) s_tw2k[i] = tw2k[i];
+  __syncthreads();
+  float acc = 0.0f;
+  const float a = 1e-3f * (float)(lane + 1), b = 1e-4f * (float)(warp + 1);
+  for (int it = 0; it < iters; ++it) {
+    float2 v[32];
+    const float t = (float)it;
+#pragma unroll
+    for (int m = 0; m < 32; ++m) v[m] = make_float2(fmaf(a, (float)m, t), fmaf(b, (float)(m * m), a));
+    core_pass1(lane, v, ex, s_tw1);
+    __syncwarp();
+    core_pass2_load(lane, v, ex);
+    __syncwarp();
+    core_pass2_fft(v);
+    core_publish_upper(lane, v, ex, true);
+    __syncwarp();
+    BinSinkT<false> o;
+    o.mag = mag;
+    split_2048(lane, v, ex, s_tw2k, o);
+    __syncwarp();
+    acc += mag[lane + 32 * (it & 31)];
+    __syncwarp();
+  }
+  if (acc == 123.456f) out[0] = acc;
+}
+}  // namespace
+
+extern "C" MMB_API int mmb_fft_probe(int32_t device, int32_t frame_size, double* frames_per_s) {
+  if (!frames_per_s) return MMB_E_INVALID;
+  *frames_per_s = 0.0;
+  if (frame_size != 2048) return MMB_E_UNSUPPORTED;
+  if (cudaSetDevice(device) != cudaSuccess) return MMB_E_CUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return MMB_E_CUDA;
+  const double PI = 3.14159265358979323846264338327950288;
+  std::vector<float2> tw1(1024), tw2k(512);
+  for (int k1 = 0; k1 < 32; ++k1)
+    for (int l = 0; l < 32; ++l) {
+      const double ang = -2.0 * PI * (double)((l * k1) % 1024) / 1024.0;
+      tw1[mmb::tw1_index(k1, l)] = make_float2((float)std::cos(ang), (float)std::sin(ang));
+    }
+  for (int k = 0; k < 512; ++k) {
+    const double ang = -2.0 * PI * (double)k / 2048.0;
+    tw2k[k] = make_float2((float)std::cos(ang), (float)std::sin(ang));
+  }
+  float2 *d1 = nullptr, *d2 = nullptr;
+  float* dout = nullptr;
+  const int smem = 8192 + 4096 + 16 * (8448 + 16);
+  int rc = MMB_OK;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (cudaMalloc(&d1, 1024 * sizeof(float2)) != cudaSuccess || cudaMalloc(&d2, 512 * sizeof(float2)) != cudaSuccess ||
+      cudaMalloc(&dout, 4) != cudaSuccess ||
+      cudaMemcpy(d1, tw1.data(), 1024 * sizeof(float2), cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaMemcpy(d2, tw2k.data(), 512 * sizeof(float2), cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaFuncSetAttribute(fft_only_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+    rc = MMB_E_CUDA;
+  } else {
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int iters = 2048, grid = prop.multiProcessorCount;
+    double best = 0.0;
+    for (int rep = 0; rep < 4 && rc == MMB_OK; ++rep) {
+      cudaEventRecord(e0);
+      fft_only_kernel<<<grid, 512, smem>>>(d1, d2, iters, dout);
+      cudaEventRecord(e1);
+      if (cudaEventSynchronize(e1) != cudaSuccess) { rc = MMB_E_CUDA; break; }
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, e0, e1);
+      const double fps = (double)iters * 16.0 * grid / (ms * 1e-3);
+      if (rep > 0 && fps > best) best = fps;
+    }
+    *frames_per_s = best;
+  }
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  cudaFree(d1); cudaFree(d2); cudaFree(dout);
+  return rc;
 }

@@ -11,6 +11,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>    // header-only NVTX v3: ranges around the entry points show up in nsys / ncu timelines
+
 #include "../../include/madmom_b200.h"
 #include "frontend_params.h"
 #include "fft_core.cuh"          // tw1_index: layout of the inter-pass twiddle table
@@ -27,6 +29,23 @@ static int cuda_fail(cudaError_t e, const char* what) {
   return fail(MMB_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 }
 #define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
+
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+
+// The entry points work on the plan's device and leave the caller's current device as they found it.
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int device) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != device) err = cudaSetDevice(device); else if (err == cudaSuccess) prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define ON_DEVICE(d) DeviceGuard guard_(d); if (guard_.err != cudaSuccess) return cuda_fail(guard_.err, "cudaSetDevice")
 
 namespace {
 // One stage of the host pipeline of mmb_run_host: its own stream and device buffers, reused from call to call.
@@ -230,6 +249,7 @@ void build_schedule(const mmb_config* cfg, int K, const std::vector<int32_t>& wo
 }  // namespace
 
 extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
+  NvtxRange nvtx_("mmb_plan_create");
   if (!cfg || !out) return fail(MMB_E_INVALID, "null argument");
   *out = nullptr;
   const int N = cfg->frame_size;
@@ -265,7 +285,8 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   p->cfg.fft_window = nullptr; p->cfg.band_start = nullptr; p->cfg.band_len = nullptr; p->cfg.band_weights = nullptr;
   p->nnz = nnz;
   p->sample_bytes = cfg->pcm_dtype == MMB_PCM_I16 ? 2 : 4;
-  cudaError_t e = cudaSetDevice(cfg->device);
+  DeviceGuard guard_(cfg->device);
+  cudaError_t e = guard_.err;
   if (e != cudaSuccess) { mmb_plan_destroy(p); return cuda_fail(e, "cudaSetDevice"); }
   cudaDeviceProp prop;
   e = cudaGetDeviceProperties(&prop, cfg->device);
@@ -412,7 +433,7 @@ extern "C" int mmb_layout_create(const mmb_plan* p, const mmb_track* units, int3
   *out = nullptr;
   int rc = validate_units(units, n);
   if (rc) return rc;
-  CU(cudaSetDevice(p->cfg.device));
+  ON_DEVICE(p->cfg.device);
   mmb_layout* l = new (std::nothrow) mmb_layout();
   if (!l) return fail(MMB_E_NOMEM, "out of host memory");
   std::vector<int32_t> prefix;
@@ -497,11 +518,12 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
 
 extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_dev, const mmb_outputs* outs,
                        void* stream, int32_t* launches) {
+  NvtxRange nvtx_("mmb_run");
   if (launches) *launches = 0;
   if (!p || !l || !pcm_dev) return fail(MMB_E_INVALID, "null argument");
   int rc = check_outputs(p, outs);
   if (rc) return rc;
-  CU(cudaSetDevice(p->cfg.device));
+  ON_DEVICE(p->cfg.device);
   int nl = 0;
   rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, outs,
               (cudaStream_t)stream, &nl);
@@ -511,6 +533,7 @@ extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_d
 
 extern "C" int mmb_run_gather(const mmb_plan* p, const mmb_layout* l, const void* pcm_dev, const mmb_outputs* dsts,
                               int32_t n_dst, void* stream, int32_t* launches) {
+  NvtxRange nvtx_("mmb_run_gather");
   if (launches) *launches = 0;
   if (!p || !l || !pcm_dev || !dsts) return fail(MMB_E_INVALID, "null argument");
   if (n_dst < 1 || n_dst > mmb::kMaxExtraDst + 1) return fail(MMB_E_INVALID, "n_dst must be in [1, 8]");
@@ -525,7 +548,7 @@ extern "C" int mmb_run_gather(const mmb_plan* p, const mmb_layout* l, const void
         (a.log && a.ld_log != b.ld_log) || (a.diff && a.ld_diff != b.ld_diff))
       return fail(MMB_E_INVALID, "every destination must hold the same outputs with the same leading dimensions");
   }
-  CU(cudaSetDevice(p->cfg.device));
+  ON_DEVICE(p->cfg.device);
   int nl = 0;
   rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, &dsts[0],
               (cudaStream_t)stream, &nl, dsts + 1, n_dst - 1);
@@ -535,13 +558,14 @@ extern "C" int mmb_run_gather(const mmb_plan* p, const mmb_layout* l, const void
 
 extern "C" int mmb_run_multicast(const mmb_plan* p, const mmb_layout* l, const void* pcm_dev, const mmb_outputs* mc,
                                  void* stream, int32_t* launches) {
+  NvtxRange nvtx_("mmb_run_multicast");
   if (launches) *launches = 0;
   if (!p || !l || !pcm_dev || !mc) return fail(MMB_E_INVALID, "null argument");
   int rc = check_outputs(p, mc);
   if (rc) return rc;
   if (mc->stft || mc->spec || mc->filt || mc->lgd)
     return fail(MMB_E_UNSUPPORTED, "mmb_run_multicast stores the band outputs log, diff and odf only");
-  CU(cudaSetDevice(p->cfg.device));
+  ON_DEVICE(p->cfg.device);
   int nl = 0;
   rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, mc,
               (cudaStream_t)stream, &nl, nullptr, 0, true);
@@ -571,6 +595,7 @@ constexpr int64_t kGroupBytes = 64ll << 20;
 
 static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, const void* pcm_host,
                          int32_t channels, int32_t channel, const mmb_outputs* oh, int32_t* launches) {
+  NvtxRange nvtx_("mmb_run_host");
   if (launches) *launches = 0;
   if (!p || !pcm_host) return fail(MMB_E_INVALID, "null argument");
   if (channels < 1 || channel < -1 || channel >= channels) return fail(MMB_E_INVALID, "bad channel count / index");
@@ -578,10 +603,11 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
   if (rc) return rc;
   rc = check_outputs(p, oh);
   if (rc) return rc;
-  CU(cudaSetDevice(p->cfg.device));
+  ON_DEVICE(p->cfg.device);
   for (int32_t i = 1; i < n; ++i)
-    if (units[i].pcm_offset < units[i - 1].pcm_offset || units[i].out_row < units[i - 1].out_row + units[i - 1].frame_count)
-      return fail(MMB_E_INVALID, "mmb_run_host needs units ordered by pcm_offset with consecutive, non-overlapping out_row ranges");
+    if (units[i].pcm_offset < units[i - 1].pcm_offset || units[i].out_row != units[i - 1].out_row + units[i - 1].frame_count)
+      return fail(MMB_E_INVALID, "mmb_run_host needs units ordered by pcm_offset with consecutive out_row ranges "
+                                 "(out_row[i] == out_row[i-1] + frame_count[i-1])");
   const int K = p->cfg.frame_size / 2 + (p->cfg.include_nyquist ? 1 : 0), B = p->cfg.num_bands;
   const size_t sb = (size_t)p->sample_bytes;
   // widths (elements) and element sizes of the six outputs: stft spec filt log diff odf

@@ -355,7 +355,8 @@ __global__ void __launch_bounds__(256, 2) complex_flux_stream_kernel(
         sig_lo = sig_hi; sig_hi = sig_lo + seg_rows;
       }
     }
-    const bool last = row + 1 >= sig_hi;                  // 'reflect': the row itself stands in for its neighbour
+    // 'reflect': the row itself stands in for its neighbour; the last signal may be shorter than seg_rows
+    const bool last = row + 1 >= sig_hi || row + 1 >= rows;
     float4* m4 = reinterpret_cast<float4*>(mx);
 #pragma unroll
     for (int j = 0; j < NV; ++j) {

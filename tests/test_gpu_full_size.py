@@ -59,6 +59,7 @@ def test_config2_logfiltspecflux_full_size(batch):
 
 
 def test_config3_multires_full_size(batch):
+    from oracle import frontend as O
     from madmom_b200 import recipe as R
     from madmom_b200.batch import BatchFrontEnd
     pcm, lengths = batch
@@ -79,6 +80,14 @@ def test_config3_multires_full_size(batch):
     for i in picks:
         alone = fe.run_device(pcm[i], [lengths[i]], ("stack",))["stack"]
         assert torch.equal(alone, stack[i * T:(i + 1) * T]), i
+        # against the oracle: the (3000, 266) stack of this track, all three frame sizes
+        x = pcm[i].cpu().numpy()
+        cols = []
+        for N in (1024, 2048, 4096):
+            st = O.run_recipe(x, dict(frame_size=N, hop_size=441., num_bands=6, norm_filters=True, mul=1, add=1,
+                                      diff_ratio=0.5, positive_diffs=True), stages=True)
+            cols += [st["log"], st["diff"]]
+        assert_close(stack[i * T:(i + 1) * T].cpu().numpy(), np.hstack(cols), what="config 3 stack, track %d" % i)
 
 
 def test_config4_ten_hour_signal_shards():

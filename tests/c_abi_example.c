@@ -10,6 +10,7 @@
  */
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "../include/madmom_b200.h"
 
@@ -53,6 +54,7 @@ int main(int argc, char** argv) {
   fclose(g);
 
   mmb_config cfg;
+  memset(&cfg, 0, sizeof(cfg));   /* fields added by later library versions default to 0 */
   cfg.frame_size = N; cfg.pcm_dtype = MMB_PCM_I16; cfg.hop_size = hop; cfg.origin = 0; cfg.circular_shift = 0;
   cfg.fft_window = win; cfg.num_bands = B; cfg.band_start = start; cfg.band_len = len; cfg.band_weights = w;
   cfg.log_mode = MMB_LOG_LOG10; cfg.mul = 1.0f; cfg.add = 1.0f;

@@ -49,7 +49,10 @@ def main():
                               norm_filters=True, unique_filters=False)
         g["mel80_N%d_dense" % N] = np.asarray(fb)                            # duplicate low bands: keep it dense
         g["mel80_N%d_center" % N] = np.asarray(fb.center_frequencies)
-    g["bark_N2048_dense"] = np.asarray(FI.BarkFilterbank(ST.fft_frequencies(1024, 44100), num_bands="normal"))
+    # the bank FilteredSpectrogram(filterbank=BarkFilterbank, num_bands='normal') builds (its own fmin / fmax defaults)
+    g["bark_N2048_dense"] = np.asarray(FI.BarkFilterbank(ST.fft_frequencies(1024, 44100), num_bands="normal",
+                                                         fmin=30., fmax=17000., norm_filters=True,
+                                                         unique_filters=True))
     sig = S.Signal(sample_file)
     g["filt_mel40"] = np.asarray(SP.FilteredSpectrogram(sample_file, filterbank=FI.MelFilterbank, num_bands=40))
     g["filt_bark"] = np.asarray(SP.FilteredSpectrogram(sample_file, filterbank=FI.BarkFilterbank,

@@ -175,6 +175,27 @@ MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg_offsets_de
                              int32_t post_avg, int32_t pre_max, int32_t post_max, int32_t* peaks_dev,
                              int32_t* counts_dev, void* stream);
 
+/* mmb_peak_picking for callers that may not allocate device memory (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same peak definition and arguments as mmb_peak_picking, but the per-frame flags, which mmb_peak_picking keeps in
+ * the caller's n-element peaks buffer, live in a static device array inside the library of
+ * MMB_STATIC_PEAK_MAX_FRAMES int32 (16 MiB, held by every GPU that loads the library until the process exits), and
+ * the output has a fixed capacity per segment: peaks_dev[s * peaks_per_segment + j], j < min(counts_dev[s],
+ * peaks_per_segment), holds the ascending local frame indices of segment s; counts_dev[s] is the number of peaks
+ * FOUND, so counts_dev[s] > peaks_per_segment tells the caller that the segment overflowed.
+ * The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine): it launches two kernels on
+ * `stream`.  The device of `stream` must be current; the first call on a device looks the array's address up
+ * (cudaGetSymbolAddress), so make one call outside a graph capture first (n = 0 is enough).
+ * n > MMB_STATIC_PEAK_MAX_FRAMES returns MMB_E_INVALID with a message.  Every call on a device shares the array; it
+ * keeps the previous call's flags, which is harmless because a call rewrites every flag it later reads, but two
+ * calls that overlap on the GPU (different streams, no dependency between them) RACE: serialise them. */
+#define MMB_STATIC_PEAK_MAX_FRAMES (1 << 22)
+MMB_API int mmb_peak_picking_static(const float* act_dev, const int64_t* seg_offsets_dev, int32_t n_segments,
+                                    int64_t n, double threshold, int32_t smooth, const double* smooth_kernel_dev,
+                                    int32_t pre_avg, int32_t post_avg, int32_t pre_max, int32_t post_max,
+                                    int32_t* peaks_dev, int32_t peaks_per_segment, int32_t* counts_dev,
+                                    void* stream);
+
 /* complex_flux() of madmom/features/onsets.py:245-317 from the lgd and diff outputs of mmb_run:
  * temporal maximum filter of width temporal_filter (odd, reflect borders inside each signal; <= 1: none) on lgd,
  * mask[b] = min over bins [band_lo[b], band_hi[b]) (the band's non-zero bins plus one either side, clipped),

@@ -74,6 +74,8 @@ EXPORTS = {
                                  c_vp, c_vp]),
     "mmb_peak_picking": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp,
                                  c_vp, c_vp]),
+    "mmb_peak_picking_static": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32,
+                                        c_vp, c_i32, c_vp, c_vp]),
 }
 
 _lib = None
@@ -423,6 +425,32 @@ def peak_picking(act, threshold, smooth=0, pre_avg=0, post_avg=0, pre_max=1, pos
         raise ValueError("mmb_peak_picking: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_peak_picking failed")
     launch_count += 2 if n else 1
     return peaks, counts
+
+
+STATIC_PEAK_MAX_FRAMES = 1 << 22
+
+
+def peak_picking_static(act, threshold, peaks, counts, smooth=0, smooth_kernel=None, pre_avg=0, post_avg=0,
+                        pre_max=1, post_max=1, seg_offsets=None):
+    """mmb_peak_picking_static: peak picking that allocates nothing.  Every buffer is the caller's: `act` float32
+    CUDA vector, `peaks` int32 CUDA tensor (n_segments, peaks_per_segment), `counts` int32 CUDA tensor (n_segments,),
+    `smooth_kernel` float64 CUDA vector of length `smooth` when smooth > 1, `seg_offsets` int64 CUDA tensor or None.
+    The flags live in a static device array of the library (at most STATIC_PEAK_MAX_FRAMES frames per call; calls
+    that overlap on the GPU race).  Asynchronous on the current stream."""
+    global launch_count
+    import torch
+    if not act.is_cuda or act.dtype != torch.float32 or act.dim() != 1 or not act.is_contiguous():
+        raise ValueError("activations must be a contiguous 1-D float32 CUDA tensor")
+    n_seg = 1 if seg_offsets is None else int(seg_offsets.shape[0]) - 1
+    if (peaks.dtype != torch.int32 or peaks.dim() != 2 or peaks.shape[0] != n_seg or not peaks.is_contiguous() or
+            counts.dtype != torch.int32 or counts.shape != (n_seg,) or not counts.is_contiguous()):
+        raise ValueError("peaks must be a contiguous (n_segments, capacity) and counts a (n_segments,) int32 tensor")
+    _check(load().mmb_peak_picking_static(act.data_ptr(), None if seg_offsets is None else seg_offsets.data_ptr(),
+                                          n_seg, act.shape[0], float(threshold), int(smooth or 0),
+                                          None if smooth_kernel is None else smooth_kernel.data_ptr(), int(pre_avg),
+                                          int(post_avg), int(pre_max), int(post_max), peaks.data_ptr(),
+                                          int(peaks.shape[1]), counts.data_ptr(), _stream(act.device.index)))
+    launch_count += 2 if act.shape[0] else 1
 
 
 def complex_flux(lgd, diff, band_lo, band_hi, temporal_filter=3, rows_per_signal=0, seg_offsets=None):

@@ -25,6 +25,8 @@ static_assert(sizeof(mmb_track) == sizeof(Track), "mmb_track layout");
 static thread_local std::string g_err;
 
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+// for the entry points that live in other translation units (postproc.cu): same thread-local message
+namespace mmb { int set_error(int code, const char* msg) { return fail(code, msg); } }
 static int cuda_fail(cudaError_t e, const char* what) {
   return fail(MMB_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 }

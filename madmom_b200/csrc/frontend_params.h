@@ -173,6 +173,9 @@ struct Stft64Params {
   float* out_spec;  int64_t ld_spec;
 };
 
+// records the message mmb_last_error() returns on the calling thread; returns `code` (capi.cu)
+int set_error(int code, const char* msg);
+
 cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, int grid, int smem_bytes,
                             cudaStream_t stream);
 cudaError_t launch_stft64(int N, int sample_bytes, const Stft64Params& p, int grid, cudaStream_t stream);

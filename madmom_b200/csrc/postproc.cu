@@ -16,6 +16,8 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "../../include/madmom_b200.h"
 #include "frontend_params.h"
 
@@ -558,6 +560,111 @@ extern "C" MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg
   }
   peak_compact_kernel<<<n_segments, 1024, 0, st>>>(p);
   return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+}
+
+// ---------------------------------------------------------------------------------------------- no-alloc peak picking
+// mmb_peak_picking_static: the variant for callers that may not allocate device memory (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  mmb_peak_picking keeps its per-frame flags in the caller's
+// n-element `peaks` buffer and compacts in place; here the flags live in a file-scope device array that every GPU
+// loading the library holds until exit (MMB_STATIC_PEAK_MAX_FRAMES int32 = 16 MiB), and the peaks of segment s go
+// to a caller buffer of fixed capacity per segment.  Has no counterpart in the reference.
+//
+// In host code `g_static_peak_flags` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current (static_peak_flags() below).
+static __device__ __align__(256) int32_t g_static_peak_flags[MMB_STATIC_PEAK_MAX_FRAMES];
+
+namespace {
+// ordered compaction of the flags of one segment into out[s * cap ...]; counts[s] is the number of peaks FOUND
+// (it may exceed cap: the caller sees that the segment overflowed; only the first cap indices are stored)
+__global__ void __launch_bounds__(1024) peak_compact_out_kernel(const int32_t* __restrict__ flags,
+                                                                const int64_t* __restrict__ seg, int64_t n,
+                                                                int32_t* __restrict__ out, int32_t cap,
+                                                                int32_t* __restrict__ counts) {
+  __shared__ int warp_tot[32];
+  __shared__ int base;
+  const int s = blockIdx.x;
+  const int64_t s0 = seg ? seg[s] : 0;
+  const int64_t len = (seg ? seg[s + 1] : n) - s0;
+  const int32_t* f_in = flags + s0;
+  int32_t* dst = out + (int64_t)s * cap;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+  for (int64_t t0 = 0; t0 < len; t0 += blockDim.x) {
+    const int64_t i = t0 + threadIdx.x;
+    const int f = (i < len) ? f_in[i] : 0;
+    const unsigned m = __ballot_sync(0xffffffffu, f != 0);
+    if (lane == 0) warp_tot[warp] = __popc(m);
+    __syncthreads();
+    int off = base;
+    for (int w = 0; w < warp; ++w) off += warp_tot[w];
+    const int at = off + __popc(m & ((1u << lane) - 1u));
+    if (f && at < cap) dst[at] = (int32_t)i;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tot = 0;
+      for (int w = 0; w < nw; ++w) tot += warp_tot[w];
+      base += tot;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) counts[s] = base;
+}
+
+// device address of the flag array on the CURRENT device; looked up once per device (no allocation: the array is
+// part of the library's device image)
+int static_peak_flags(int32_t** out) {
+  constexpr int kMaxDevices = 64;
+  static int32_t* ptrs[kMaxDevices] = {nullptr};
+  static std::mutex mu;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices)
+    return mmb::set_error(MMB_E_CUDA, "mmb_peak_picking_static: no current CUDA device");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_peak_flags);
+    if (e != cudaSuccess || !p)
+      return mmb::set_error(MMB_E_CUDA, "mmb_peak_picking_static: cudaGetSymbolAddress(g_static_peak_flags) failed");
+    ptrs[dev] = static_cast<int32_t*>(p);
+  }
+  *out = ptrs[dev];
+  return MMB_OK;
+}
+}  // namespace
+
+extern "C" MMB_API int mmb_peak_picking_static(const float* act_dev, const int64_t* seg_offsets_dev,
+                                               int32_t n_segments, int64_t n, double threshold, int32_t smooth,
+                                               const double* smooth_kernel_dev, int32_t pre_avg, int32_t post_avg,
+                                               int32_t pre_max, int32_t post_max, int32_t* peaks_dev,
+                                               int32_t peaks_per_segment, int32_t* counts_dev, void* stream) {
+  if ((!act_dev && n > 0) || !peaks_dev || !counts_dev || n < 0 || n_segments < 1 || pre_avg < 0 || post_avg < 0 ||
+      pre_max < 0 || post_max < 0 || smooth < 0 || (smooth > 1 && !smooth_kernel_dev) ||
+      (n_segments > 1 && !seg_offsets_dev) || peaks_per_segment < 1)
+    return mmb::set_error(MMB_E_INVALID, "mmb_peak_picking_static: invalid argument");
+  if (n > (int64_t)MMB_STATIC_PEAK_MAX_FRAMES)
+    return mmb::set_error(MMB_E_INVALID,
+                          "mmb_peak_picking_static: more than MMB_STATIC_PEAK_MAX_FRAMES (4194304) frames in one "
+                          "call; the static scratch array cannot hold their flags (use mmb_peak_picking)");
+  int32_t* flags = nullptr;
+  const int rc = static_peak_flags(&flags);
+  if (rc != MMB_OK) return rc;
+  PeakParams p;
+  p.act = act_dev; p.seg = seg_offsets_dev; p.n = n; p.n_seg = n_segments; p.threshold = threshold;
+  p.smooth = smooth; p.pre_avg = pre_avg; p.post_avg = post_avg; p.pre_max = pre_max; p.post_max = post_max;
+  p.kernel = smooth_kernel_dev; p.peaks = flags; p.counts = counts_dev;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n > 0) {
+    // the flag kernel writes flags[i] for every i < n, so nothing of the previous call's contents survives in the
+    // range this call reads: the array needs no clearing
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (smooth > 1) peak_flag_kernel<double><<<grid, 256, 0, st>>>(p);
+    else peak_flag_kernel<float><<<grid, 256, 0, st>>>(p);
+  }
+  peak_compact_out_kernel<<<n_segments, 1024, 0, st>>>(flags, seg_offsets_dev, n, peaks_dev, peaks_per_segment,
+                                                       counts_dev);
+  if (cudaGetLastError() != cudaSuccess) return mmb::set_error(MMB_E_CUDA, "mmb_peak_picking_static: kernel launch failed");
+  return MMB_OK;
 }
 
 extern "C" MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, const float* diff_dev, int64_t ld_diff,

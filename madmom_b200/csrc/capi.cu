@@ -343,6 +343,8 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   for (int w = wmax; w >= 1 && p->warps == 0; --w) {
     const int gw = (gw_req > 0 && gw_req <= w) ? gw_req : w;
     if (w % gw != 0 || (w / gw > 15 && gw > 1)) continue;      // named barriers 1 .. 15, one per group
+    // N = 4096: two warps per frame, and their pair barriers take the ids behind the groups' (2 .. 15)
+    if (N == 4096 && (gw % 2 != 0 || w / gw + w / 2 > 15)) continue;
     const int fpr = mmb::frames_per_round(N, gw);
     const int span = (((int)std::ceil((fpr - 1) * cfg->hop_size) + 2 + N + align_elems) + 7) & ~7;
     const int rows = 2 * fpr + cfg->diff_frames;

@@ -160,11 +160,14 @@ __device__ __forceinline__ void frames_loaded(const FrontendParams& p, GroupCtl*
 // warp's scratch, then the per-band sum of pieces, log scaling and the ring row.  `mag1` is the second frame of a
 // 1024-point pair or null.
 // SPLIT: the magnitudes are stored as even bins in `mag0` and odd bins in `mag1` (N = 4096).
+// The warp takes the passes ps0, ps0 + ps_step, ...: the two warps of a 4096-point frame share the passes of one
+// frame (ps0 = 0 / 1, ps_step = 2) and write into one set of partial sums.
 template <int NF, bool SPLIT = false>
 __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lane, const float* __restrict__ mag0,
                                                 const float* __restrict__ mag1, float* part,
                                                 const FbPass* __restrict__ s_pass, const float* __restrict__ s_w,
-                                                const int* __restrict__ s_start, const int* __restrict__ s_pid) {
+                                                const int* __restrict__ s_start, const int* __restrict__ s_pid,
+                                                int ps0 = 0, int ps_step = 1) {
   // the previous frame's epilogue reads of `part` are complete: the warp has passed a __syncwarp since
   const int np1 = p.max_q * p.b_pad + 1;
   if (p.L.part_stride == 0) {          // the slots share memory with the FFT exchange tile: clear them per frame
@@ -172,7 +175,7 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
     for (int i = lane; i < n4; i += 32) reinterpret_cast<float4*>(part)[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     __syncwarp();
   }
-  for (int ps = 0; ps < p.n_passes; ++ps) {
+  for (int ps = ps0; ps < p.n_passes; ps += ps_step) {
     const FbPass fp = s_pass[ps];
     const int st = s_start[ps * 32 + lane];
     const float4* w = reinterpret_cast<const float4*>(s_w + fp.woff) + lane;
@@ -218,9 +221,10 @@ __device__ __forceinline__ void warp_filterbank(const FrontendParams& p, int lan
 
 // rows of the ring / outputs for one frame g handled by this warp
 __device__ __forceinline__ void warp_band_epilogue(const FrontendParams& p, int lane, const float* part,
-                                                   float* ring_row, long long row, bool emit) {
+                                                   float* ring_row, long long row, bool emit, int b0 = 0,
+                                                   int b_step = 32) {
   const int nb = p.n_bands, bp = p.b_pad, nq = p.max_q;
-  for (int b = lane; b < nb; b += 32) {
+  for (int b = b0 + lane; b < nb; b += b_step) {
     // pieces are added in order q = 0, 1, ...; slots without a piece stay zero.  The first four loads are issued
     // together (the piece count is warp-uniform), the rare longer tails in a loop.
     const float* pp = part + b;
@@ -347,10 +351,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
 
   unsigned char* my_scratch = smem + L.scratch + warp * warp_scratch_bytes(N);
   float2* ex = reinterpret_cast<float2*>(my_scratch);
-  float* my_mag = reinterpret_cast<float*>(my_scratch);                       // odd bins for N = 4096
-  float* my_mag_even = reinterpret_cast<float*>(my_scratch + kEvenMagOffset);   // N = 4096 only
+  float* my_mag = reinterpret_cast<float*>(my_scratch);     // N = 4096: even bins in warp 2f, odd bins in warp 2f + 1
+  // N = 4096: the magnitude arrays of this warp's pair and the pair's barrier (ids behind the groups' barriers)
+  const float* pair_even = reinterpret_cast<const float*>(smem + L.scratch + (warp & ~1) * warp_scratch_bytes(N));
+  const float* pair_odd = reinterpret_cast<const float*>(smem + L.scratch + (warp | 1) * warp_scratch_bytes(N));
+  const int pair_bar = 1 + warps / GW + (warp >> 1);
   float* my_part = L.part_stride == 0 ? reinterpret_cast<float*>(my_scratch + kPartAliasOffset)
-                                      : reinterpret_cast<float*>(smem + L.part + warp * L.part_stride);
+                                      : reinterpret_cast<float*>(smem + L.part + (warp / part_sharers(N)) * L.part_stride);
 
   // ---- plan constants -> shared memory (once per persistent CTA)
   for (int i = tid; i < N; i += nthreads) s_win[i] = p.win[i];
@@ -365,7 +372,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     for (int i = tid; i < p.n_passes; i += nthreads) s_pass[i] = p.fb_pass[i];
     for (int i = tid; i < p.w_floats; i += nthreads) s_w[i] = p.fb_w[i];
     for (int i = tid; i < p.n_passes * 32; i += nthreads) { s_start[i] = p.fb_start[i]; s_pid[i] = p.fb_pid[i]; }
-    for (int i = tid; i < warps * (L.part_stride / 4); i += nthreads)     // private slots only
+    for (int i = tid; i < (warps / part_sharers(N)) * (L.part_stride / 4); i += nthreads)     // private slots only
       reinterpret_cast<float*>(smem + L.part)[i] = 0.0f;     // part slots without a piece are never written again
   }
   uint64_t* ring_bar = reinterpret_cast<uint64_t*>(&G->ring_bar);
@@ -473,12 +480,46 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           MMB_ROWS_WRITTEN();
         }
       }
+    } else if (N == 4096) {
+      // two warps per frame: the radix-2 pre-stage splits the packed 2048-point sequence into the half that gives the
+      // even bins (warp 2f, c = 0) and the one that gives the odd bins (warp 2f + 1, c = 1); each is a 1024-point
+      // complex FFT of its own.  The pair meets twice: before the filterbank (both magnitude arrays are in place;
+      // each warp then takes every other pass) and after it (all partial sums of the frame are written).
+      const int f = gwarp >> 1, c = gwarp & 1;
+      if (f >= nfr) {
+        frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+        if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
+      } else {
+        const S* x = span0 + (int)(frame_start_sample(D->g0 + f, p.hop, N, p.origin) - D->s_begin);
+        load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
+        frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+        core_pass1(lane, v, ex, s_tw1);
+        __syncwarp();
+        core_pass2_load(lane, v, ex);
+        __syncwarp();
+        core_pass2_fft(v);
+        core_publish_upper(lane, v, ex, c == 0);
+        __syncwarp();
+        BinSinkT<false> o;
+        o.mag = my_mag;
+        split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
+        if (nb > 0) {
+          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+          warp_filterbank<1, true>(p, lane, pair_even, pair_odd, my_part, s_pass, s_w, s_start, s_pid, c, 2);
+          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+          MMB_PENDING_DIFFERENCE();
+          const long long g = D->g0 + f;
+          int sl = D->slot0 + f; if (sl >= R) sl -= R;
+          warp_band_epilogue(p, lane, my_part, s_ring + sl * nb, D->row0 + g, g >= D->ga, 32 * c, 64);
+          MMB_ROWS_WRITTEN();
+        }
+      }
     } else if (gwarp >= nfr) {
       frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
       if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
     } else {
       const S* x = span0 + (int)(frame_start_sample(D->g0 + gwarp, p.hop, N, p.origin) - D->s_begin);
-      if (N == 2048) {
+      {
         load_frame_2048<S>(lane, v, x, s_win);
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
         core_pass1(lane, v, ex, s_tw1);
@@ -497,28 +538,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         } else {
           split_2048(lane, v, ex, s_tw2k, o);
         }
-      } else {
-#pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-          load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
-          if (c == 1) frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
-          core_pass1(lane, v, ex, s_tw1);
-          __syncwarp();
-          core_pass2_load(lane, v, ex);
-          __syncwarp();
-          core_pass2_fft(v);
-          core_publish_upper(lane, v, ex, c == 0);
-          __syncwarp();
-          BinSinkT<false> o;
-          o.mag = c == 0 ? my_mag_even : my_mag;
-          split_4096(lane, c, v, ex, s_tw2k, s_tw4k, o);
-          __syncwarp();
-        }
       }
       if (nb > 0) {
         __syncwarp();
-        if (N == 4096) warp_filterbank<1, true>(p, lane, my_mag_even, my_mag, my_part, s_pass, s_w, s_start, s_pid);
-        else warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
+        warp_filterbank<1>(p, lane, my_mag, nullptr, my_part, s_pass, s_w, s_start, s_pid);
         MMB_PENDING_DIFFERENCE();
         const long long g = D->g0 + gwarp;
         int sl = D->slot0 + gwarp; if (sl >= R) sl -= R;

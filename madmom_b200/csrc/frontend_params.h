@@ -92,15 +92,21 @@ constexpr int kMaxWarps = 16;
 constexpr int kMaxDiffFrames = 16;
 
 // frames one round of a warp group produces
-__host__ __device__ constexpr int frames_per_round(int N, int group_warps) { return N == 1024 ? 2 * group_warps : group_warps; }
-// per-warp scratch (bytes): exchange tile with the magnitudes aliased in its lower 4 KB.  N = 4096 keeps the even
-// bins (first half of the frame's two FFT calls) in 4 KB behind the tile, 16 floats off so that even and odd
-// bins of neighbouring lanes fall into different banks, and the odd bins in the tile like the other sizes.
-constexpr int kEvenMagOffset = 8448 + 64;
+// (N = 1024: two frames per warp, packed into one complex FFT; N = 4096: two warps per frame, one per half of the
+// radix-2 pre-stage)
+__host__ __device__ constexpr int frames_per_round(int N, int group_warps) {
+  return N == 1024 ? 2 * group_warps : (N == 4096 ? group_warps / 2 : group_warps);
+}
+// per-warp scratch (bytes): exchange tile with the magnitudes aliased in its lower 4 KB.  N = 4096: the two warps of
+// a frame keep the even bins (warp 2j) and the odd bins (warp 2j + 1) in their own tiles; the scratch is 16 floats
+// longer so that the two arrays lie 16 banks apart and even / odd bins of neighbouring lanes fall into different
+// banks.
 // the exchange tile above the 4 KB of magnitudes is idle between the split and the next frame's FFT: the partial
 // sums of the filterbank may live there when that buys another warp (they must then be cleared per frame)
 constexpr int kPartAliasOffset = 4096, kPartAliasBytes = 8448 - 4096;
-__host__ __device__ constexpr int warp_scratch_bytes(int N) { return (N == 4096 ? kEvenMagOffset + 4096 : 8448) + 16; }
+__host__ __device__ constexpr int warp_scratch_bytes(int N) { return 8448 + (N == 4096 ? 64 : 16); }
+// warps that share one set of filterbank partial sums
+__host__ __device__ constexpr int part_sharers(int N) { return N == 4096 ? 2 : 1; }
 
 // one descriptor per round of a group, written by one lane, read by the group (4 slots, see frontend_kernel.cu)
 struct RoundDesc {
@@ -150,8 +156,10 @@ inline SmemLayout smem_layout(int N, int warps, int group_warps, int n_bands, in
   L.ring = o;        o += groups * L.ring_stride;
   L.scratch = o;     o += warps * warp_scratch_bytes(N);
   L.part_stride = mmb_align16((part_floats + 1) * 4 * (N == 1024 ? 2 : 1));
-  if (alias_part && L.part_stride <= kPartAliasBytes) L.part_stride = 0;
-  L.part = o;        o += n_bands > 0 ? warps * L.part_stride : 0;
+  // (a pair of warps of a 4096-point frame shares one private set: clearing an aliased one would race with the
+  //  partner's epilogue of the frame before)
+  if (alias_part && N != 4096 && L.part_stride <= kPartAliasBytes) L.part_stride = 0;
+  L.part = o;        o += n_bands > 0 ? (warps / part_sharers(N)) * L.part_stride : 0;
   L.pcm_stride = mmb_align16(span_cap * sample_bytes);
   L.pcm = o;         o += groups * L.pcm_stride;
   L.total = o;

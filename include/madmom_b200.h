@@ -247,7 +247,8 @@ MMB_API int mmb_measure_fp32_peak(int32_t device, double* tflops);
 
 /* Instruction-rate probes behind the issue-slot roofline in DESIGN.md: which = 1 FFMA with three register
  * operands, 2 FADD, 3 FMUL+FADD pairs, 4 LDS.64 + 2 FFMA, 5 LDS.32, 6 SHFL, 7 LDS.32 + SHFL, 8 FADD2 (f32x2),
- * 9 FFMA2 (f32x2), 10 FFMA2 + LDS.32 + FADD.  *ginst_per_s = 1e9 thread-level FP instructions
+ * 9 FFMA2 (f32x2), 10 FFMA2 + LDS.32 + FADD, 11 LDS.64, 12 LDS.128, 13 STS.64 + LDS.64, 14 STS.64 (one step of
+ * 11 .. 14 counts as one instruction).  *ginst_per_s = 1e9 thread-level FP instructions
  * per second over the whole device. */
 MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s);
 

@@ -92,6 +92,23 @@ __global__ void __launch_bounds__(256) rate_probe(float* out, int iters, float a
         else asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(p), "l"(q), "l"(q));
         asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[i]), "=f"(y[i]) : "l"(r));
         if (WHICH == 10) acc[i] += reinterpret_cast<const float*>(sm)[(threadIdx.x + 32 * i + it) & 1023];
+      } else if (WHICH == 11) {          // LDS.64, conflict-free: 2 wavefronts per instruction
+        const float2 w = sm[(threadIdx.x + 32 * i + it) & 511];
+        acc[i] += w.x + w.y;
+      } else if (WHICH == 12) {          // LDS.128, conflict-free: 4 wavefronts per instruction
+        const float4 w = reinterpret_cast<const float4*>(sm)[(threadIdx.x + 32 * i + it) & 255];
+        acc[i] += (w.x + w.y) + (w.z + w.w);
+      } else if (WHICH == 13) {          // STS.64 then LDS.64 of another slot (the FFT exchange pattern)
+        const unsigned a0 = (unsigned)__cvta_generic_to_shared(&sm[(threadIdx.x + 32 * i) & 511]);
+        const unsigned a1 = (unsigned)__cvta_generic_to_shared(&sm[(threadIdx.x + 32 * i + 7) & 511]);
+        float wx, wy;
+        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a0), "f"(acc[i]), "f"(x[i]) : "memory");
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(wx), "=f"(wy) : "r"(a1) : "memory");
+        acc[i] += wx + wy;
+      } else if (WHICH == 14) {          // STS.64 only
+        const unsigned a0 = (unsigned)__cvta_generic_to_shared(&sm[(threadIdx.x + 32 * i + it) & 511]);
+        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a0), "f"(acc[i]), "f"(x[i]) : "memory");
+        acc[i] += x[i];
       } else if (WHICH == 7) {           // one LDS.32 + one SHFL per step
         acc[i] = __shfl_sync(0xffffffffu, acc[i], (threadIdx.x + i + 1) & 31) +
                  reinterpret_cast<const float*>(sm)[(threadIdx.x + 32 * i + it) & 1023];
@@ -108,7 +125,7 @@ __global__ void __launch_bounds__(256) rate_probe(float* out, int iters, float a
 // result: warp-level FP instructions per clock per SM at the current clock estimate is left to the caller;
 // *ginst_per_s receives 1e9 thread-level FP instructions per second (whole device).
 extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s) {
-  if (!ginst_per_s || which < 1 || which > 10) return MMB_E_INVALID;
+  if (!ginst_per_s || which < 1 || which > 14) return MMB_E_INVALID;
   if (cudaSetDevice(device) != cudaSuccess) return MMB_E_CUDA;
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return MMB_E_CUDA;
@@ -129,7 +146,11 @@ extern "C" MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* gin
     else if (which == 7) rate_probe<7><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     else if (which == 8) rate_probe<8><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     else if (which == 9) rate_probe<9><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
-    else rate_probe<10><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 10) rate_probe<10><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 11) rate_probe<11><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 12) rate_probe<12><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else if (which == 13) rate_probe<13><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    else rate_probe<14><<<grid, 256>>>(d, iters, 1.0000001f, 1e-9f);
     cudaEventRecord(e1);
     if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return MMB_E_CUDA; }
     float ms = 0.f;

@@ -511,6 +511,16 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   fp.out_lgd = o->lgd; fp.ld_lgd = o->ld_lgd;
   fp.n_extra = n_extra; fp.multicast = multicast ? 1 : 0;
   for (int t = 0; t < n_extra; ++t) { fp.x_log[t] = extra[t].log; fp.x_diff[t] = extra[t].diff; fp.x_odf[t] = extra[t].odf; }
+  if (n_extra > 0 || multicast) {
+    // 16-byte gathered stores: ring rows (n_bands floats each) and every destination row must start on 16 bytes
+    bool ok = fp.n_bands % 4 == 0 && (!o->log || o->ld_log % 4 == 0) && (!o->diff || o->ld_diff % 4 == 0) &&
+              p->L.ring % 16 == 0 && p->L.ring_stride % 16 == 0;
+    auto aligned = [](const void* q) { return q == nullptr || ((uintptr_t)q % 16) == 0; };
+    ok = ok && aligned(o->log) && aligned(o->diff);
+    for (int t = 0; t < n_extra; ++t) ok = ok && aligned(extra[t].log) && aligned(extra[t].diff);
+    if (const char* env = std::getenv("MMB_GATHER_VEC")) ok = ok && std::atoi(env) != 0;      // experiments
+    fp.gather_vec = ok ? 1 : 0;
+  }
   const int groups = p->warps / p->group_warps;
   int grid = p->num_sms;                              // one persistent CTA per SM
   if (grid > (chunks + groups - 1) / groups) grid = (chunks + groups - 1) / groups;

@@ -248,51 +248,90 @@ __device__ __forceinline__ void mc_store(float* a, float v) {
   asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
 }
 
+__device__ __forceinline__ void mc_store4(float* a, float4 v) {
+  asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// difference value of band b: cur[b] - max over the frequency window of prev (scipy maximum_filter, 'reflect'),
+// optionally rectified; 0 for the first d frames of a signal
+__device__ __forceinline__ float band_difference(const FrontendParams& p, const float* cur, const float* prev,
+                                                 bool has_prev, int b, int nb) {
+  if (!has_prev) return 0.0f;
+  const int m = p.max_bins;
+  float ref;
+  if (m == 3) {                                          // the SuperFlux case, 'reflect' duplicates the edge bin
+    ref = fmaxf(fmaxf(prev[b > 0 ? b - 1 : 0], prev[b]), prev[b + 1 < nb ? b + 1 : nb - 1]);
+  } else if (m > 1) {                                    // scipy maximum_filter, mode='reflect'
+    const int half = m / 2;
+    ref = -INFINITY;
+    for (int j = 0; j < m; ++j) {
+      int q = b - half + j;
+      q = q < 0 ? -q - 1 : (q >= nb ? 2 * nb - q - 1 : q);
+      ref = fmaxf(ref, prev[q]);
+    }
+  } else {
+    ref = prev[b];
+  }
+  const float dv = cur[b] - ref;
+  return p.positive ? fmaxf(dv, 0.0f) : dv;
+}
+
 // lagged difference of frame g against the ring row of frame g - d (phase C)
 // GATHER: the launch also stores to peer / multicast destinations (mmb_run_gather, mmb_run_multicast); the plain
-// launches are a separate instantiation without that code (it cost them 4 % when it was a runtime branch)
+// launches are a separate instantiation without that code (it cost them 4 % when it was a runtime branch).
+// Remote rows go out as 16 bytes per lane when the host found everything aligned (p.gather_vec): a lane then owns
+// four consecutive bands, recomputed with the same operations as in the lane = band mapping of the local row and
+// of the flux, so every destination receives the same bits; a warp store covers 512 contiguous bytes of the peer's
+// row instead of 128.
 template <bool GATHER>
 __device__ __forceinline__ void warp_difference(const FrontendParams& p, int lane, const float* cur,
                                                 const float* prev, bool has_prev, long long row) {
   const int nb = p.n_bands, nx = GATHER ? p.n_extra : 0;
   const bool mc = GATHER && p.multicast != 0;
+  const bool vec = GATHER && p.gather_vec != 0;
   if (p.out_log) {
     float* o = p.out_log + row * p.ld_log;
-    if (mc) for (int b = lane; b < nb; b += 32) mc_store(o + b, cur[b]);
-    else for (int b = lane; b < nb; b += 32) o[b] = cur[b];
-    for (int t = 0; t < nx; ++t) {                       // fused all-gather: the same row into the peers' matrices
-      float* ox = p.x_log[t] + row * p.ld_log;
-      for (int b = lane; b < nb; b += 32) ox[b] = cur[b];
+    if (mc && vec) {
+      for (int b = 4 * lane; b < nb; b += 128) mc_store4(o + b, *reinterpret_cast<const float4*>(cur + b));
+    } else if (mc) {
+      for (int b = lane; b < nb; b += 32) mc_store(o + b, cur[b]);
+    } else {
+      for (int b = lane; b < nb; b += 32) o[b] = cur[b];
+    }
+    if (vec) {
+      for (int b = 4 * lane; b < nb; b += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(cur + b);
+        for (int t = 0; t < nx; ++t) *reinterpret_cast<float4*>(p.x_log[t] + row * p.ld_log + b) = v;
+      }
+    } else {
+      for (int t = 0; t < nx; ++t) {                     // fused all-gather: the same row into the peers' matrices
+        float* ox = p.x_log[t] + row * p.ld_log;
+        for (int b = lane; b < nb; b += 32) ox[b] = cur[b];
+      }
     }
   }
   if (p.out_diff == nullptr && p.out_odf == nullptr) return;
   float sum = 0.0f;
-  const int m = p.max_bins, half = m / 2;
   for (int b = lane; b < nb; b += 32) {
-    float dv = 0.0f;
-    if (has_prev) {
-      float ref;
-      if (m == 3) {                                      // the SuperFlux case, 'reflect' duplicates the edge bin
-        ref = fmaxf(fmaxf(prev[b > 0 ? b - 1 : 0], prev[b]), prev[b + 1 < nb ? b + 1 : nb - 1]);
-      } else if (m > 1) {                                // scipy maximum_filter, mode='reflect'
-        ref = -INFINITY;
-        for (int j = 0; j < m; ++j) {
-          int q = b - half + j;
-          q = q < 0 ? -q - 1 : (q >= nb ? 2 * nb - q - 1 : q);
-          ref = fmaxf(ref, prev[q]);
-        }
-      } else {
-        ref = prev[b];
-      }
-      dv = cur[b] - ref;
-      if (p.positive) dv = fmaxf(dv, 0.0f);
-    }
+    const float dv = band_difference(p, cur, prev, has_prev, b, nb);
     if (p.out_diff) {
-      if (mc) mc_store(p.out_diff + row * p.ld_diff + b, dv);
+      if (mc) { if (!vec) mc_store(p.out_diff + row * p.ld_diff + b, dv); }
       else p.out_diff[row * p.ld_diff + b] = dv;
-      for (int t = 0; t < nx; ++t) p.x_diff[t][row * p.ld_diff + b] = dv;
+      if (!vec) for (int t = 0; t < nx; ++t) p.x_diff[t][row * p.ld_diff + b] = dv;
     }
     sum += dv;
+  }
+  if (vec && p.out_diff) {
+    for (int b = 4 * lane; b < nb; b += 128) {
+      float4 v;
+      v.x = band_difference(p, cur, prev, has_prev, b, nb);
+      v.y = band_difference(p, cur, prev, has_prev, b + 1, nb);
+      v.z = band_difference(p, cur, prev, has_prev, b + 2, nb);
+      v.w = band_difference(p, cur, prev, has_prev, b + 3, nb);
+      if (mc) mc_store4(p.out_diff + row * p.ld_diff + b, v);
+      for (int t = 0; t < nx; ++t) *reinterpret_cast<float4*>(p.x_diff[t] + row * p.ld_diff + b) = v;
+    }
   }
   if (p.out_odf) {
 #pragma unroll

@@ -83,6 +83,8 @@ struct FrontendParams {
   // (peer memory of the other ranks over NVLink), same leading dimensions as the local matrices
   int32_t n_extra;
   int32_t multicast;             // out_log / out_diff / out_odf are NVLS multicast addresses: stored with multimem.st
+  int32_t gather_vec;            // gathered rows may be stored 16 bytes per lane: bands, leading dimensions and all
+                                 // destination pointers are multiples of four floats / 16 bytes (checked on the host)
   float* x_log[kMaxExtraDst];
   float* x_diff[kMaxExtraDst];
   float* x_odf[kMaxExtraDst];

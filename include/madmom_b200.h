@@ -257,6 +257,12 @@ MMB_API int mmb_rate_probe(int32_t device, int32_t which, double* ginst_per_s);
  * no PCM staging, window, filterbank, difference or stores).  bench.py reports the fused kernel against it. */
 MMB_API int mmb_fft_probe(int32_t device, int32_t frame_size, double* frames_per_s);
 
+/* Design probe: the per-frame work of the fused kernel (staged-sample and window loads, warp FFT, split, magnitudes,
+ * a filterbank-like pass, log / difference-like arithmetic) as mode 0: 16 warps that each do everything, mode 1: 12
+ * FFT warps + 12 light warps with their register budgets moved by setmaxnreg.  Synthetic data, no hand-off
+ * synchronisation; frames per second of the mix. */
+MMB_API int mmb_pipeline_probe(int32_t device, int32_t mode, double* frames_per_s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,7 @@ EXPORTS = {
     "mmb_measure_fp32_peak": (c_i32, [c_i32, ctypes.POINTER(c_f64)]),
     "mmb_rate_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
     "mmb_fft_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
+    "mmb_pipeline_probe": (c_i32, [c_i32, c_i32, ctypes.POINTER(c_f64)]),
     "mmb_matrix_diff": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i32, c_i64, c_i32, c_i32, c_i32, c_vp]),
     "mmb_complex_flux": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_i32, c_i32, c_i64, c_i64, c_vp, c_i32, c_i32,
                                  c_vp, c_vp]),

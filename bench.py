@@ -488,6 +488,7 @@ def run_ours(args):
                 configs[name] = {"ms_per_step": ms, "value": fr / f2.recipes[0].fps / (ms * 1e-3),
                                  "gpu_launches_per_step": nl // 4, "frames_per_step": fr,
                                  "fp32_frac": roof["frac"], "hbm_frac": roof["hbm"]["frac"],
+                                 "dram_traffic_bytes_per_step": roof["traffic"],
                                  "flops_per_frame": roof["flops_per_frame"],
                                  "algorithmic_bytes_per_frame": roof["hbm"]["algorithmic_bytes_per_frame"],
                                  "outputs": {k: list(v.shape) for k, v in o.items()}}

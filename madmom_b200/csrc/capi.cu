@@ -607,6 +607,40 @@ constexpr int64_t kGroupBytes = 64ll << 20;
 
 }  // namespace
 
+// A unit whose PCM alone exceeds a pipeline group (one long file) would pass through mmb_run_host as a single
+// host-to-device copy, kernel and copy back, one after the other.  It is cut into frame ranges of about half a
+// group, each with the PCM its frames touch: the lead-in frames of the lagged difference on the left (one more for
+// frame_size 1024, whose frames are paired by their global index) and frame_size / 2 on the right -- what
+// FramedSignal.__getitem__(slice) means (madmom/audio/signal.py:1181-1194) and what the multi-GPU shards do
+// (madmom_b200/parallel.py).  Frame starts use the global frame index, so the rows are bit-identical to the unsplit run.
+static void split_long_units(const mmb_plan* p, const mmb_track* u, int32_t n, int64_t group_bytes,
+                             std::vector<mmb_track>& out) {
+  const int N = p->cfg.frame_size;
+  const double hop = p->cfg.hop_size;
+  const int64_t sb = p->sample_bytes;
+  const int64_t lead = p->cfg.diff_frames + (N == 1024 ? 1 : 0);
+  int64_t nf = (int64_t)((double)(group_bytes / 2 / sb) / hop) & ~(int64_t)1;
+  if (nf < 64) nf = 64;
+  out.clear();
+  for (int32_t i = 0; i < n; ++i) {
+    const mmb_track& t = u[i];
+    if (t.pcm_len * sb <= group_bytes || t.frame_count <= nf) { out.push_back(t); continue; }
+    for (int64_t f = 0; f < t.frame_count; f += nf) {
+      const int64_t f0 = t.frame_first + f, f1 = std::min(f0 + nf, t.frame_first + t.frame_count);
+      const int64_t gl = std::max<int64_t>(f0 - lead, 0);
+      const int64_t base = (int64_t)(N / 2) + (int64_t)p->cfg.origin + t.sample_base;
+      int64_t lo = (int64_t)((double)gl * hop) - base;
+      int64_t hi = (int64_t)((double)(f1 - 1) * hop) - base + N;
+      lo = std::min(std::max<int64_t>(lo, 0), t.pcm_len);
+      hi = std::min(std::max<int64_t>(hi, lo), t.pcm_len);
+      mmb_track s;
+      s.pcm_offset = t.pcm_offset + lo; s.pcm_len = hi - lo; s.sample_base = t.sample_base + lo;
+      s.frame_first = f0; s.frame_count = f1 - f0; s.out_row = t.out_row + (f0 - t.frame_first);
+      out.push_back(s);
+    }
+  }
+}
+
 static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, const void* pcm_host,
                          int32_t channels, int32_t channel, const mmb_outputs* oh, int32_t* launches) {
   NvtxRange nvtx_("mmb_run_host");
@@ -635,6 +669,9 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
   // the plan's own pipeline buffers when no other thread is using them, else temporary ones
   int64_t group_bytes = kGroupBytes;
   if (const char* env = std::getenv("MMB_HOST_GROUP_MB")) group_bytes = std::max(1, std::atoi(env)) * (1ll << 20);
+  std::vector<mmb_track> split;
+  split_long_units(p, units, n, group_bytes, split);
+  units = split.data(); n = (int32_t)split.size();
   Slot local[kSlots];
   std::unique_lock<std::mutex> lock(p->pipe->mu, std::try_to_lock);
   Slot* slots = lock.owns_lock() ? p->pipe->slots : local;

@@ -253,6 +253,29 @@ def test_host_path_equals_device_path():
     assert np.array_equal(odf, dev["odf"])
 
 
+@pytest.mark.parametrize("N,ratio", [(2048, 0.5), (1024, 0.5), (4096, 0.25)])
+def test_host_path_splits_a_long_unit(N, ratio, monkeypatch):
+    """A unit larger than a pipeline group (one long file) is cut into frame ranges with their PCM halo inside
+    mmb_run_host so that copies and kernels overlap; rows stay bit-identical to the device path (frame starts by the
+    global index, lead-in frames recomputed; frame pairing of N = 1024 included).  A short unit before and after
+    the long one, an odd number of samples, the group size forced down to 1 MiB."""
+    from madmom_b200 import _lib
+    from madmom_b200.synth import make_track
+    tracks = [make_track(70 + i, num_samples=n) for i, n in enumerate([30001, 44100 * 100 + 77, 5000])]
+    plan, _ = _plan_for(np.int16, N, 441., 6, True, ratio=ratio)
+    dev, T = _run_all(plan, tracks, 441.)
+    units = _lib.make_units([len(t) for t in tracks], T)
+    rows = sum(T)
+    pcm = np.concatenate(tracks)
+    monkeypatch.setenv("MMB_HOST_GROUP_MB", "1")
+    out = {"log": np.zeros((rows, plan.num_bands), np.float32), "diff": np.full((rows, plan.num_bands), np.nan, np.float32),
+           "odf": np.zeros(rows, np.float32), "spec": np.zeros((rows, plan.num_bins), np.float32)}
+    n = plan.run_host(pcm, units, out)
+    assert n >= 8                                        # the 8.8 MB unit went through as several groups
+    for k in out:
+        assert np.array_equal(out[k], dev[k]), (N, k)
+
+
 def test_errors():
     from madmom_b200 import _lib
     with pytest.raises(NotImplementedError):

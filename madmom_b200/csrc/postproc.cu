@@ -238,7 +238,8 @@ __global__ void __launch_bounds__(256) complex_flux_kernel(const float* __restri
       const int s = find_segment(seg, n_seg, row);
       s0 = seg[s]; len = seg[s + 1] - s0;
     } else if (seg_rows > 0) {
-      s0 = (row / seg_rows) * seg_rows; len = seg_rows;
+      s0 = (row / seg_rows) * seg_rows;
+      len = seg_rows < rows - s0 ? seg_rows : rows - s0;     // the last signal may be shorter
     }
     const int64_t t = row - s0;
     // rows of the temporal neighbourhood ('reflect': (b a | a b c))

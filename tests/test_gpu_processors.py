@@ -532,7 +532,7 @@ def test_complex_flux_kernel_ragged_signals(n_bins, monkeypatch):
     monkeypatch.delenv("MMB_CF_GENERIC")
     # equal-length signals by rows_per_signal, and one signal only
     lgd2, diff2 = t(lgd[:1000]), t(diff[:1000])
-    for rps in (0, 8, 250):
+    for rps in (0, 8, 250, 300, 999):                 # 300, 999: the last signal is shorter than rows_per_signal
         a = _lib.complex_flux(lgd2, diff2, args[2], args[3], rows_per_signal=rps).cpu().numpy()
         monkeypatch.setenv("MMB_CF_GENERIC", "1")
         b_ = _lib.complex_flux(lgd2, diff2, args[2], args[3], rows_per_signal=rps).cpu().numpy()

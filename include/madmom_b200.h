@@ -206,6 +206,12 @@ MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, const float* 
                              int64_t rows, int64_t rows_per_signal, const int64_t* seg_offsets_dev, int32_t n_segments,
                              int32_t temporal_filter, float* odf_dev, void* stream);
 
+/* phase() and local_group_delay() of madmom/audio/stft.py:136-179 (the Phase / LocalGroupDelay classes, :556-708) on a
+ * complex64 STFT on the device (rows x cols, re / im pairs): phase = angle(stft); lgd[:, k] = unwrap(phase)[k] -
+ * unwrap(phase)[k + 1] with numpy's unwrap rule, last column 0.  Either output may be null. */
+MMB_API int mmb_phase_lgd(const void* stft_dev, int64_t ld_stft, float* phase_dev, int64_t ld_phase, float* lgd_dev,
+                          int64_t ld_lgd, int64_t rows, int32_t cols, void* stream);
+
 /* PCM ingest (madmom/audio/signal.py:170-223 `remix`, called from Signal.__new__ :600-632): interleaved
  * (num_frames, num_channels) int16 (sample_bytes 2) or float32 (4) on the device -> mono of the same type.
  * channel = -1: mean over the channels with the reference's rounding (np.mean(..., axis=-1).astype(dtype): integer

@@ -75,6 +75,7 @@ EXPORTS = {
                                  c_vp, c_vp]),
     "mmb_peak_picking": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp,
                                  c_vp, c_vp]),
+    "mmb_phase_lgd": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_i32, c_vp]),
     "mmb_peak_picking_static": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_f64, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32,
                                         c_vp, c_i32, c_vp, c_vp]),
 }
@@ -502,6 +503,21 @@ def spectral_odf(mode, stft=None, spec=None, diff_frames=1, epsilon=2.2204460492
         raise ValueError("mmb_spectral_odf: invalid argument") if rc == MMB_E_INVALID else LibraryError("mmb_spectral_odf failed")
     launch_count += 1 if rows else 0
     return odf
+
+
+def phase_lgd(stft, want_phase=True, want_lgd=False):
+    """mmb_phase_lgd on a (rows, cols) complex64 CUDA tensor: (phase or None, lgd or None), float32 on the device."""
+    global launch_count
+    import torch
+    if not stft.is_cuda or stft.dtype != torch.complex64 or stft.dim() != 2 or stft.stride(1) != 1:
+        raise ValueError("stft must be a 2-D complex64 CUDA tensor with contiguous columns")
+    rows, cols = stft.shape
+    ph = torch.empty((rows, cols), dtype=torch.float32, device=stft.device) if want_phase else None
+    lg = torch.empty((rows, cols), dtype=torch.float32, device=stft.device) if want_lgd else None
+    _check(load().mmb_phase_lgd(stft.data_ptr(), stft.stride(0), ph.data_ptr() if want_phase else None, cols,
+                                lg.data_ptr() if want_lgd else None, cols, rows, cols, _stream(stft.device.index)))
+    launch_count += 1 if rows else 0
+    return ph, lg
 
 
 def remix_mono(pcm, channel=None):

@@ -164,8 +164,100 @@ class ShortTimeFourierTransform(DeviceResult):
         from .spectrogram import Spectrogram
         return Spectrogram(self, **kwargs)
 
+    def phase(self, **kwargs):
+        return Phase(self, **kwargs)
+
 
 STFT = ShortTimeFourierTransform
+
+
+def phase(stft):
+    """Phase of a complex STFT, np.angle (madmom/audio/stft.py:136-151).  Device results stay on the device."""
+    if isinstance(stft, ShortTimeFourierTransform):
+        return Phase(stft)
+    return np.angle(stft)
+
+
+def local_group_delay(phase):
+    """Local group delay of a phase matrix: unwrap along the bins, lgd[:, k] = up[k] - up[k + 1], last bin 0
+    (madmom/audio/stft.py:154-179).  A `Phase` object is answered on the device, a plain array on the host."""
+    if isinstance(phase, Phase):
+        return LocalGroupDelay(phase)
+    phase = np.asarray(phase)
+    if phase.ndim != 2:
+        raise ValueError("phase must be a 2D array")
+    up = np.unwrap(phase)
+    up[:, :-1] -= up[:, 1:]
+    up[:, -1] = 0
+    return up
+
+
+lgd = local_group_delay
+
+
+class Phase(DeviceResult):
+    """np.angle of the STFT, (num_frames, num_bins) float32 (madmom/audio/stft.py:556-642).  Built from anything a
+    ShortTimeFourierTransform can be built from; `circular_shift` then defaults to True, and an STFT without it
+    draws the reference's RuntimeWarning."""
+
+    def __init__(self, stft, **kwargs):
+        import warnings
+        if isinstance(stft, Phase):
+            stft = stft.stft
+        if not isinstance(stft, ShortTimeFourierTransform):
+            circular_shift = kwargs.pop("circular_shift", True)
+            stft = ShortTimeFourierTransform(stft, circular_shift=circular_shift, **kwargs)
+        if not stft.circular_shift:
+            warnings.warn("`circular_shift` of the STFT must be set to 'True' for correct phase", RuntimeWarning)
+        DeviceResult.__init__(self, stft._chain.copy())
+        self.stft = stft
+
+    def _compute(self):
+        from .. import _lib
+        return _lib.phase_lgd(self.stft.tensor, want_phase=True, want_lgd=False)[0]
+
+    def _shape(self):
+        return self.stft.shape
+
+    @property
+    def bin_frequencies(self):
+        return self.stft.bin_frequencies
+
+    def local_group_delay(self, **kwargs):
+        return LocalGroupDelay(self, **kwargs)
+
+    lgd = local_group_delay
+
+
+class LocalGroupDelay(DeviceResult):
+    """Local group delay of the phase of an STFT (madmom/audio/stft.py:646-708): unwrapped phase differences along
+    the bins, last bin 0.  Computed from the complex bins directly (the difference of neighbouring unwrapped phases
+    is the wrapped phase difference), so it does not carry the rounding of the reference's float32 cumulative sum
+    (up to about 4e-5)."""
+
+    def __init__(self, phase, **kwargs):
+        import warnings
+        if not isinstance(phase, Phase):
+            phase = Phase(phase, circular_shift=True, **kwargs)
+        if not phase.stft.circular_shift:
+            warnings.warn("`circular_shift` of the STFT must be set to 'True' for correct local group delay")
+        DeviceResult.__init__(self, phase._chain.copy())
+        self.phase = phase
+        self.stft = phase.stft
+
+    def _compute(self):
+        from .. import _lib
+        return _lib.phase_lgd(self.stft.tensor, want_phase=False, want_lgd=True)[1]
+
+    def _shape(self):
+        return self.stft.shape
+
+    @property
+    def bin_frequencies(self):
+        return self.stft.bin_frequencies
+
+
+LGD = LocalGroupDelay
 
 
 class ShortTimeFourierTransformProcessor(Processor):

@@ -563,6 +563,53 @@ extern "C" MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg
   return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
 }
 
+// ---------------------------------------------------------------------------------------------- phase / local group delay
+// phase()  = np.angle(stft)                                          (madmom/audio/stft.py:136-151)
+// local_group_delay() = unwrap(phase) along the bins, lgd[:, k] = up[k] - up[k + 1], last bin 0    (:154-179)
+// The difference of neighbouring unwrapped phases needs no scan: up[k] - up[k+1] = -(dd + correction) with
+// dd = p[k+1] - p[k] and numpy's unwrap rule  ddmod = mod(dd + pi, 2 pi) - pi,  ddmod = pi where it came out as -pi for
+// dd > 0,  correction = ddmod - dd where |dd| >= pi, else 0.
+namespace {
+__global__ void __launch_bounds__(256) phase_lgd_kernel(const float2* __restrict__ stft, int64_t ld_stft,
+                                                        float* __restrict__ phase, int64_t ld_phase,
+                                                        float* __restrict__ lgd, int64_t ld_lgd, int64_t rows,
+                                                        int32_t cols) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * cols) return;
+  const int64_t row = i / cols;
+  const int k = (int)(i - row * cols);
+  const float2 z = stft[row * ld_stft + k];
+  const float p0 = atan2f(z.y, z.x);
+  if (phase) phase[row * ld_phase + k] = p0;
+  if (lgd) {
+    float v = 0.0f;
+    if (k + 1 < cols) {
+      const float pi = 3.14159265358979323846f, two_pi = 6.28318530717958647692f;
+      const float2 z1 = stft[row * ld_stft + k + 1];
+      const float dd = atan2f(z1.y, z1.x) - p0;
+      float ddmod = fmodf(dd + pi, two_pi);
+      if (ddmod < 0.0f) ddmod += two_pi;                 // np.mod: result has the sign of the divisor
+      ddmod -= pi;
+      if (ddmod == -pi && dd > 0.0f) ddmod = pi;
+      v = fabsf(dd) < pi ? -dd : -ddmod;
+    }
+    lgd[row * ld_lgd + k] = v;
+  }
+}
+}  // namespace
+
+extern "C" MMB_API int mmb_phase_lgd(const void* stft_dev, int64_t ld_stft, float* phase_dev, int64_t ld_phase,
+                                     float* lgd_dev, int64_t ld_lgd, int64_t rows, int32_t cols, void* stream) {
+  if (!stft_dev || (!phase_dev && !lgd_dev) || rows < 0 || cols < 1 || ld_stft < cols ||
+      (phase_dev && ld_phase < cols) || (lgd_dev && ld_lgd < cols))
+    return mmb::set_error(MMB_E_INVALID, "mmb_phase_lgd: invalid argument");
+  if (rows == 0) return MMB_OK;
+  const int64_t n = rows * cols;
+  phase_lgd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      (const float2*)stft_dev, ld_stft, phase_dev, ld_phase, lgd_dev, ld_lgd, rows, cols);
+  return cudaGetLastError() == cudaSuccess ? MMB_OK : mmb::set_error(MMB_E_CUDA, "mmb_phase_lgd: kernel launch failed");
+}
+
 // ---------------------------------------------------------------------------------------------- no-alloc peak picking
 // mmb_peak_picking_static: the variant for callers that may not allocate device memory (CUDA graph capture, tight
 // serving loops, harnesses that forbid cudaMalloc).  mmb_peak_picking keeps its per-frame flags in the caller's

@@ -117,6 +117,10 @@ __global__ void __launch_bounds__(256) stft64_kernel(const Stft64Params p) {
         const double2 w = p.tw[k];
         re = ar + (br * w.x - bi * w.y);
         im = ai + (br * w.y + bi * w.x);
+        // X[0] is real.  The sign of its zero imaginary part decides between +pi and -pi in np.angle of a negative
+        // sum: scipy.fftpack, the backend of the pinned oracle, returns -0.0 (pyfftw, which the reference's docstrings
+        // were made with, +0.0); follow the oracle.
+        if (k == 0) im = -0.0;
       }
       const float rf = (float)re, imf = (float)im;            // the reference's complex64 store
       if (p.out_stft) p.out_stft[row * p.ld_stft + k] = make_float2(rf, imf);

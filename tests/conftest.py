@@ -51,6 +51,11 @@ def ref_mel():
 
 
 @pytest.fixture(scope="session")
+def ref_phase():
+    return _npz("ref_phase.npz")
+
+
+@pytest.fixture(scope="session")
 def ref_odfs():
     return _npz("ref_odfs.npz")
 

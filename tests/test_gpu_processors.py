@@ -411,6 +411,46 @@ def test_complex_flux(sig, ref_sample):
                                                 0.0954693183], atol=2e-5)
 
 
+def test_phase_and_local_group_delay(sig, ref_phase):
+    """Phase / LocalGroupDelay (madmom/audio/stft.py:556-708) against rows computed by the real reference
+    (tests/golden/make_golden_phase.py): the phase to 2e-6 rad modulo 2 pi (the bins come from the float64 kernel),
+    the local group delay to 1e-4 (the reference's float32 cumulative unwrap carries up to about 4e-5 of rounding;
+    here it is the wrapped phase difference itself).  circular_shift defaults to True when the STFT is built by
+    Phase; an STFT without it draws the reference's warning; chaining and aliases as in the reference."""
+    import warnings
+    from madmom_b200.audio.stft import (ShortTimeFourierTransform, Phase, LocalGroupDelay, LGD, phase,
+                                        local_group_delay)
+    rows = ref_phase["rows"]
+
+    def wrapped(a, b):
+        d = np.abs(a.astype(np.float64) - b.astype(np.float64))
+        return np.minimum(d, 2 * np.pi - d)
+    ph = Phase(sig)
+    assert ph.stft.circular_shift and ph.shape == (281, 1024) and ph.dtype == np.float32
+    assert wrapped(np.asarray(ph)[rows], ref_phase["phase_rows"]).max() <= 2e-6
+    lg = ph.lgd()
+    assert isinstance(lg, LocalGroupDelay) and LGD is LocalGroupDelay and lg.stft is ph.stft and lg.phase is ph
+    assert lg.shape == (281, 1024) and not np.asarray(lg)[:, -1].any()
+    assert wrapped(np.asarray(lg)[rows], ref_phase["lgd_rows"]).max() <= 1e-4
+    assert wrapped(np.asarray(LocalGroupDelay(sig))[rows], ref_phase["lgd_rows"]).max() <= 1e-4
+    assert np.allclose(ph.bin_frequencies, ph.stft.bin_frequencies)
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        plain = Phase(ShortTimeFourierTransform(sig))                  # no circular shift: the docstring's example
+        assert any(issubclass(x.category, RuntimeWarning) for x in w)
+    assert wrapped(np.asarray(plain)[rows], ref_phase["phase_plain_rows"]).max() <= 2e-6
+    # bin 0 is real: +pi for a negative sum like np.angle gives, not -pi
+    for got, want in ((np.asarray(plain)[rows], ref_phase["phase_plain_rows"]),
+                      (np.asarray(ph)[rows], ref_phase["phase_rows"])):
+        assert np.array_equal(got[:, 0], want[:, 0])
+    # function forms and the method on the STFT
+    assert np.array_equal(np.asarray(phase(ph.stft)), np.asarray(ph))
+    assert np.array_equal(np.asarray(local_group_delay(ph)), np.asarray(lg))
+    assert np.array_equal(np.asarray(ph.stft.phase()), np.asarray(ph))
+    with pytest.raises(ValueError):
+        local_group_delay(np.arange(10))
+
+
 @pytest.mark.parametrize("which", ["sample", "synth"])
 def test_other_spectral_odfs(sample_pcm, ref_odfs, which):
     """the remaining onset detection functions of madmom/features/onsets.py, with the inputs the

@@ -391,3 +391,16 @@ def test_synthetic_tracks(ref_synth):
         assert np.allclose(multires_oracle(x, 1, 0.5), ref_synth[tag + "_rnn_beat"], rtol=1e-6, atol=1e-6)
     xf = make_track(1000, 3.0, dtype=np.float32)
     assert np.allclose(O.run_recipe(xf, O.SUPERFLUX), ref_synth["s1000_f32_superflux"], rtol=1e-6, atol=1e-6)
+
+
+def test_phase_and_local_group_delay_vs_reference(ref_phase):
+    """oracle.phase / oracle.local_group_delay (madmom/audio/stft.py:136-179) on the reference's own STFT rows equal
+    the reference's Phase / LocalGroupDelay rows; literals of tests/test_audio_stft.py:141-147."""
+    from oracle import frontend as O
+    ph = O.phase(ref_phase["stft_rows"])
+    assert ph.dtype == np.float32 and np.array_equal(ph, ref_phase["phase_rows"])
+    assert np.array_equal(O.local_group_delay(ph), ref_phase["lgd_rows"])
+    assert np.array_equal(ref_phase["lgd_rows"], ref_phase["lgd_from_class_rows"])
+    assert np.allclose(O.local_group_delay(np.arange(20).reshape(10, 2) * 2), np.tile([-2, 0], 10).reshape(10, 2))
+    assert np.allclose(O.local_group_delay(np.arange(20).reshape(10, 2) * 4),
+                       np.tile([2.28318531, 0], 10).reshape(10, 2))

@@ -67,8 +67,12 @@ def make_batch_torch(n_tracks, seconds=30.0, sample_rate=SAMPLE_RATE, device="cu
         for k in range(20):
             env = bamp[:, k:k + 1] * torch.exp(-ar[None, :] / decay[:, k:k + 1])
             noise = torch.randn((nb, ln), device=device, generator=g)
-            idx = (starts[:, k:k + 1] + torch.arange(ln, device=device)[None, :]).clamp_(max=n - 1)
-            x.scatter_add_(1, idx, env * noise)
+            idx = starts[:, k:k + 1] + torch.arange(ln, device=device)[None, :]
+            # a burst that runs past the end of the track is cut off: its tail is zeroed before the indices are
+            # clamped, so the colliding atomic adds on the last sample all add 0.0 and the result does not depend on
+            # their order (the same seed then gives the same samples on every rank and in every run)
+            burst = (env * noise) * (idx < n)
+            x.scatter_add_(1, idx.clamp_(max=n - 1), burst)
         out[b0:b0 + nb] = x.round_().clamp_(-32768, 32767).to(torch.int16)
     if dtype is not None and dtype != torch.int16:
         return (out.to(torch.float32) / 32767.).to(dtype)

@@ -582,7 +582,7 @@ def run_long_signal(torch, dist, dev, local, world, rank, barrier, max_over_rank
     # same samples on every device), then every rank keeps only its slice
     whole = make_batch_torch(minutes, 60.0, device=dev, seed=7).reshape(-1)
     if world > 1:
-        dist.broadcast(whole, src=0)
+        dist.broadcast(whole.view(torch.uint8), src=0)        # NCCL has no int16: the bytes travel
     n = whole.numel()
     fe = parallel.LongSignalFrontEnd(R.SUPERFLUX, device=local)
     shard = fe.shard(n, world, rank)

@@ -392,6 +392,159 @@ __global__ void __launch_bounds__(256, 2) complex_flux_stream_kernel(
   }
 }
 
+// Cover variant (round 2), the one mmb_complex_flux launches for temporal_filter = 3 and 512 / 1024 bins: the
+// streaming kernel above with the serial walk over a band's bins (up to 47 dependent shared-memory reads per band of
+// the 24-bands-per-octave bank, 93 loop iterations per row) replaced by a hierarchical minimum.
+//   * A lane's float4 of maxima gives the minimum of its aligned 4-bin block for free, two shuffles give the aligned
+//     16-bin block; maxima and block minima go to the warp's shared row S = [bins | 4-blocks | 16-blocks].
+//   * Every band's bin range [lo, hi) is covered once, when the CTA starts, by the largest aligned blocks that fit
+//     (at most 3 + 3 + n16 + 3 + 3 entries; 3 - 14 for that bank) and stored as 16-bit byte offsets into S, kCfcCover
+//     per band, unused entries repeating the last one (the minimum does not mind), 48 bytes per band so that the
+//     lanes' 16-byte table reads fall into different banks.  Lane l owns the bands l, l + 32, ... as before; a group
+//     of 32 bands makes as many reads as its longest cover has entries (5 + 5 + 8 + 10 + 14 = 42 for that bank).
+//   * Same summation order as the other two kernels: results are bit-identical
+//     (tests/test_gpu_processors.py::test_complex_flux_kernel_ragged_signals compares the three).
+// A band whose cover does not fit (wider than about 200 bins) makes the CTA fall back to the serial walk.
+// A CTA-per-run variant (thread = four bins, three rows in 12 registers, 32 warps per SM, two __syncthreads per
+// row) was built first and measured at 3.5 - 5.3 ms per 1.536 M rows against 2.6 ms for the streaming kernel: ncu
+// shows 7.9 of 8 warps per scheduler waiting at the barriers (5 of 8 warps take the band minima, 1 of 8 adds the row
+// up) -- the warp-synchronous layout is the better one (profiles/r2a_sensitivity.txt).
+constexpr int kCfcCover = 24;                   // cover entries per band (48 bytes)
+constexpr int kCfcMaxGroups = 8;                // groups of 32 bands: at most 256 bands
+
+template <int NV, int NG>                        // NV float4 per lane and row, NG >= groups of 32 bands
+__global__ void __launch_bounds__(256, 2) complex_flux_cover_kernel(
+    const float* __restrict__ lgd, int64_t ld_lgd, const float* __restrict__ diff, int64_t ld_diff,
+    const int32_t* __restrict__ band_lo, const int32_t* __restrict__ band_hi, int32_t n_bands, int64_t rows,
+    int64_t seg_rows, const int64_t* __restrict__ seg, int32_t n_seg, int64_t run, float* __restrict__ odf) {
+  extern __shared__ float4 s_dyn4[];            // [warps][S], cover table [groups * 32][24] u16, group lengths, flag
+  constexpr int n_bins = 128 * NV, o4 = n_bins, o16 = o4 + n_bins / 4, s_words = o16 + n_bins / 16;
+  float* s_dyn = reinterpret_cast<float*>(s_dyn4);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  const int groups = (n_bands + 31) >> 5;
+  uint16_t* s_cover = reinterpret_cast<uint16_t*>(s_dyn + (size_t)warps * s_words);
+  int* s_glen = reinterpret_cast<int*>(s_cover + (size_t)groups * 32 * kCfcCover);     // [groups] longest cover
+  int* s_lo = s_glen + groups;                                                          // serial fallback only
+  int* s_len = s_lo + n_bands;
+  int* s_flag = s_len + n_bands;
+  for (int g = threadIdx.x; g < groups; g += blockDim.x) s_glen[g] = 0;
+  if (threadIdx.x == 0) s_flag[0] = 0;
+  __syncthreads();
+  for (int b = threadIdx.x; b < groups * 32; b += blockDim.x) {
+    const int lo = b < n_bands ? band_lo[b] : 0, hi = b < n_bands ? band_hi[b] : 0;
+    if (b < n_bands) { s_lo[b] = lo; s_len[b] = hi > lo ? hi - lo : 0; }
+    uint16_t* c = s_cover + (size_t)b * kCfcCover;
+    int n = 0, last = hi > lo ? lo : 0;
+    for (int k = lo; k < hi; ++n) {
+      int off, step;
+      if ((k & 15) == 0 && k + 16 <= hi) { off = o16 + (k >> 4); step = 16; }
+      else if ((k & 3) == 0 && k + 4 <= hi) { off = o4 + (k >> 2); step = 4; }
+      else { off = k; step = 1; }
+      if (n < kCfcCover) c[n] = (uint16_t)(4 * off);
+      last = off;
+      k += step;
+    }
+    if (n > kCfcCover) s_flag[0] = 1;
+    for (int j = n; j < kCfcCover; ++j) c[j] = (uint16_t)(4 * last);
+    atomicMax(&s_glen[b >> 5], n < kCfcCover ? n : kCfcCover);
+  }
+  __syncthreads();
+  const bool serial = s_flag[0] != 0;
+  float* mx = s_dyn + (size_t)warp * s_words;
+  const int64_t first = ((int64_t)blockIdx.x * warps + warp) * run;
+  if (first >= rows) return;
+  const int64_t stop = first + run < rows ? first + run : rows;
+
+  // [sig_lo, sig_hi): rows of the signal the current row belongs to
+  int64_t sig_lo = 0, sig_hi = rows;
+  int si = 0;
+  if (seg) {
+    si = find_segment(seg, n_seg, first);
+    sig_lo = seg[si]; sig_hi = seg[si + 1];
+  } else if (seg_rows > 0) {
+    sig_lo = (first / seg_rows) * seg_rows; sig_hi = sig_lo + seg_rows;
+  }
+  float4 P[NV], A[NV], B[NV];
+  cf_load_row<NV>(A, lgd + first * ld_lgd, lane);
+  if (first > sig_lo) cf_load_row<NV>(P, lgd + (first - 1) * ld_lgd, lane);
+  else {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) P[j] = A[j];
+  }
+  if (first + 1 < rows) cf_load_row<NV>(B, lgd + (first + 1) * ld_lgd, lane);
+  float4* m4 = reinterpret_cast<float4*>(mx);
+  const char* mxb = reinterpret_cast<const char*>(mx);       // the cover table holds byte offsets
+
+  for (int64_t row = first; row < stop; ++row) {
+    if (row >= sig_hi) {                                  // first row of the next signal
+      if (seg) {
+        do { ++si; } while (seg[si + 1] <= row);          // empty signals have no rows
+        sig_lo = seg[si]; sig_hi = seg[si + 1];
+      } else {
+        sig_lo = sig_hi; sig_hi = sig_lo + seg_rows;
+      }
+    }
+    // prefetches hold no registers: the lgd row three ahead goes to L2 (one 128-byte line per lane), the diff row
+    // two ahead to L1 (the band loop below would otherwise wait for DRAM once per group of 32 bands)
+    if (row + 3 < rows && row + 2 < stop && lane < NV * 4)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(lgd + (row + 3) * ld_lgd + 32 * lane));
+    if (row + 2 < stop && 32 * lane < n_bands)
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(diff + (row + 2) * ld_diff + 32 * lane));
+    // 'reflect': the row itself stands in for its neighbour; the last signal may be shorter than seg_rows
+    const bool last = row + 1 >= sig_hi || row + 1 >= rows;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float4 m = fmax4(P[j], A[j]);
+      if (!last) m = fmax4(m, B[j]);
+      m4[lane + 32 * j] = m;
+      float q = fminf(fminf(m.x, m.y), fminf(m.z, m.w));
+      mx[o4 + lane + 32 * j] = q;
+      q = fminf(q, __shfl_xor_sync(0xffffffffu, q, 1));
+      q = fminf(q, __shfl_xor_sync(0xffffffffu, q, 2));
+      if ((lane & 3) == 0) mx[o16 + (lane >> 2) + 8 * j] = q;
+    }
+    // shift the window and put the row after next in flight
+#pragma unroll
+    for (int j = 0; j < NV; ++j) { P[j] = last ? B[j] : A[j]; A[j] = B[j]; }
+    if (row + 2 < rows && row + 1 < stop) cf_load_row<NV>(B, lgd + (row + 2) * ld_lgd, lane);
+    __syncwarp();
+    float sum = 0.0f;
+    const float* drow = diff + row * ld_diff;
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+      if (32 * g >= n_bands) break;                       // warp-uniform
+      const int b = 32 * g + lane;
+      const bool have = b < n_bands;
+      const float d = have ? drow[b] : 0.0f;
+      float m = INFINITY;
+      if (!serial) {
+        const int glen = s_glen[g];
+        const uint4* c = reinterpret_cast<const uint4*>(s_cover + (size_t)b * kCfcCover);
+#pragma unroll
+        for (int j0 = 0; j0 < kCfcCover; j0 += 8) {
+          if (j0 >= glen) break;                          // warp-uniform
+          const uint4 o = c[j0 >> 3];
+          auto at = [&](uint32_t byte) { return *reinterpret_cast<const float*>(mxb + byte); };
+          m = fminf(m, fminf(fminf(at(o.x & 0xffffu), at(o.x >> 16)), fminf(at(o.y & 0xffffu), at(o.y >> 16))));
+          if (j0 + 4 < glen)
+            m = fminf(m, fminf(fminf(at(o.z & 0xffffu), at(o.z >> 16)), fminf(at(o.w & 0xffffu), at(o.w >> 16))));
+        }
+        sum = __fmaf_rn(d, have && s_len[b] > 0 ? m : 0.0f, sum);
+      } else {
+        const int lo = have ? s_lo[b] : 0, len = have ? s_len[b] : 0;
+        const int wlen = __reduce_max_sync(0xffffffffu, len);
+        const int top = lo + (len > 0 ? len - 1 : 0);
+        for (int k = 0; k < wlen; ++k) m = fminf(m, mx[min(lo + k, top)]);
+        sum = __fmaf_rn(d, len > 0 ? m : 0.0f, sum);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) odf[row] = sum;
+    __syncwarp();                                         // the row buffer is overwritten by the next row
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- spectral ODFs
 // One warp per frame: a reduction over the bins of a magnitude spectrogram and / or a complex STFT with lags
 // of one or two frames (madmom/features/onsets.py:102-160, 320-581).  Frames before the start of the row's signal
@@ -732,6 +885,30 @@ extern "C" MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, co
   // rows read once (streaming kernel) when the rows can be held as float4 registers
   const bool vec_ok = temporal_filter == 3 && (n_bins == 512 || n_bins == 1024) && ld_lgd % 4 == 0 &&
                       (reinterpret_cast<uintptr_t>(lgd_dev) & 15) == 0 && getenv("MMB_CF_GENERIC") == nullptr;
+  // the streaming kernel with hierarchical band minima (complex_flux_cover_kernel); MMB_CF_STREAM=1 keeps the serial
+  // walk over the bins (the tests compare the two bit for bit)
+  if (vec_ok && n_bands <= 32 * kCfcMaxGroups && getenv("MMB_CF_STREAM") == nullptr) {
+    const int groups = (n_bands + 31) / 32;
+    const size_t s_words = (size_t)n_bins + n_bins / 4 + n_bins / 16;
+    const size_t smem = (size_t)warps * s_words * sizeof(float) + (size_t)groups * 32 * kCfcCover * sizeof(uint16_t) +
+                        ((size_t)groups + 2 * (size_t)n_bands + 1) * sizeof(int);
+    auto kern = n_bins == 1024
+                    ? (groups <= 3 ? complex_flux_cover_kernel<8, 3>
+                                   : (groups <= 5 ? complex_flux_cover_kernel<8, 5> : complex_flux_cover_kernel<8, 8>))
+                    : (groups <= 3 ? complex_flux_cover_kernel<4, 3>
+                                   : (groups <= 5 ? complex_flux_cover_kernel<4, 5> : complex_flux_cover_kernel<4, 8>));
+    if (smem > 48 * 1024 &&
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+      return MMB_E_CUDA;
+    const int64_t total_warps = (int64_t)sms * 2 * warps;          // two CTAs per SM
+    const int64_t run = (rows + total_warps - 1) / total_warps;
+    const int64_t used = (rows + run - 1) / run;
+    const unsigned grid = (unsigned)((used + warps - 1) / warps);
+    kern<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(lgd_dev, ld_lgd, diff_dev, ld_diff, band_lo_dev,
+                                                           band_hi_dev, n_bands, rows, rows_per_signal,
+                                                           seg_offsets_dev, n_segments, run, odf_dev);
+    return cudaGetLastError() == cudaSuccess ? MMB_OK : MMB_E_CUDA;
+  }
   if (vec_ok) {
     const size_t smem = ((size_t)warps * n_bins + 2 * (size_t)n_bands) * sizeof(float);
     auto kern = n_bins == 1024 ? complex_flux_stream_kernel<8> : complex_flux_stream_kernel<4>;

@@ -534,17 +534,20 @@ def test_pcm_ingest_remix():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n_bins", [1024, 512, 640])
-def test_complex_flux_kernel_ragged_signals(n_bins, monkeypatch):
+@pytest.mark.parametrize("n_bins,B", [(1024, 77), (512, 77), (640, 77), (2048, 77), (512, 100), (1024, 128), (1024, 140),
+                                      (2048, 200)])
+def test_complex_flux_kernel_ragged_signals(n_bins, B, monkeypatch):
     """mmb_complex_flux on random matrices with signals of 1, 2, 3 and many rows back to back (temporal 'reflect'
-    maximum inside each signal, madmom/features/onsets.py:282-317): the streaming kernel (rows read once) and the
-    generic kernel give the same bits, and both match scipy's maximum_filter + the per-band minimum."""
+    maximum inside each signal, madmom/features/onsets.py:282-317): the block kernel (one CTA per run of rows,
+    hierarchical band minima; four, two or one lane per band depending on bins and bands), the streaming kernel
+    (one warp per row) and the generic kernel give the same bits, and match scipy's maximum_filter + the per-band
+    minimum.  Band 7 is wide enough to overflow the block kernel's register cover (its scan path)."""
     torch = pytest.importorskip("torch")
     from scipy.ndimage import maximum_filter
     from madmom_b200 import _lib
-    rng = np.random.default_rng(n_bins)
+    rng = np.random.default_rng(n_bins + B)
     lens = [1, 2, 3, 1, 57, 700, 2, 333, 1]
-    rows, B = sum(lens), 77
+    rows = sum(lens)
     lgd = rng.random((rows, n_bins), dtype=np.float32)
     diff = rng.random((rows, B), dtype=np.float32)
     centres = np.unique(np.round(np.geomspace(2, n_bins - 3, B + 2)).astype(np.int64))
@@ -553,6 +556,7 @@ def test_complex_flux_kernel_ragged_signals(n_bins, monkeypatch):
         c0 = centres[min(b, len(centres) - 3)]; c2 = centres[min(b, len(centres) - 3) + 2]
         lo[b], hi[b] = max(c0 - 1, 0), min(c2 + 2, n_bins)
     hi[5] = lo[5]                                                    # an empty band contributes nothing
+    lo[7], hi[7] = 3, n_bins - 5                                     # a cover of more than 16 / 32 blocks
     seg = np.concatenate(([0], np.cumsum(lens))).astype(np.int64)
     want = np.zeros(rows, np.float64)
     for s in range(len(lens)):
@@ -564,17 +568,27 @@ def test_complex_flux_kernel_ragged_signals(n_bins, monkeypatch):
     dev = torch.device("cuda:0")
     t = lambda x: torch.from_numpy(x).to(dev)
     args = (t(lgd), t(diff), t(lo), t(hi))
+
+    def other(env, **kw):
+        monkeypatch.setenv(env, "1")
+        try:
+            return _lib.complex_flux(*kw.pop("args", args), **kw).cpu().numpy()
+        finally:
+            monkeypatch.delenv(env)
+
     got = _lib.complex_flux(*args, seg_offsets=t(seg)).cpu().numpy()
     assert np.allclose(got, want, rtol=1e-5, atol=1e-5)
-    monkeypatch.setenv("MMB_CF_GENERIC", "1")
-    generic = _lib.complex_flux(*args, seg_offsets=t(seg)).cpu().numpy()
-    assert np.array_equal(got, generic)
-    monkeypatch.delenv("MMB_CF_GENERIC")
+    assert np.array_equal(got, other("MMB_CF_GENERIC", seg_offsets=t(seg)))
+    assert np.array_equal(got, other("MMB_CF_STREAM", seg_offsets=t(seg)))      # generic again for 640 / 2048 bins
     # equal-length signals by rows_per_signal, and one signal only
-    lgd2, diff2 = t(lgd[:1000]), t(diff[:1000])
+    args2 = (t(lgd[:1000]), t(diff[:1000]), args[2], args[3])
     for rps in (0, 8, 250, 300, 999):                 # 300, 999: the last signal is shorter than rows_per_signal
-        a = _lib.complex_flux(lgd2, diff2, args[2], args[3], rows_per_signal=rps).cpu().numpy()
-        monkeypatch.setenv("MMB_CF_GENERIC", "1")
-        b_ = _lib.complex_flux(lgd2, diff2, args[2], args[3], rows_per_signal=rps).cpu().numpy()
-        monkeypatch.delenv("MMB_CF_GENERIC")
-        assert np.array_equal(a, b_), rps
+        a = _lib.complex_flux(*args2, rows_per_signal=rps).cpu().numpy()
+        assert np.array_equal(a, other("MMB_CF_GENERIC", args=args2, rows_per_signal=rps)), rps
+        assert np.array_equal(a, other("MMB_CF_STREAM", args=args2, rows_per_signal=rps)), rps
+    # a run boundary in every position relative to a signal: 70 000 rows in signals of 37 (the block kernel's runs
+    # are 64 rows or longer)
+    big_l, big_d = t(np.tile(lgd, (64, 1))[:70000].copy()), t(np.tile(diff, (64, 1))[:70000].copy())
+    args3 = (big_l, big_d, args[2], args[3])
+    a = _lib.complex_flux(*args3, rows_per_signal=37).cpu().numpy()
+    assert np.array_equal(a, other("MMB_CF_GENERIC", args=args3, rows_per_signal=37))

@@ -20,7 +20,8 @@ through the hot path once.  Prints ONE JSON line (rank 0):
   configs      (N = 1) short timings of the other BASELINE configurations with both fractions
   long_signal  (N > 1) BASELINE config 4 on a shortened signal: NCCL all-gather vs the fused peer-store / multicast
                kernels, bit-identity of the three and of the unsharded launch
-  host_link    (N > 1) aggregate pinned-copy GB/s of all ranks copying at once: H2D only, D2H only, both
+  host_link    aggregate pinned-copy GB/s of all ranks copying at once: H2D only, D2H only, both; the e2e blocks
+               carry their own H2D rate and its fraction of this link (`h2d_gbs`, `link_frac`)
   cpu_baseline the reference's own classes (copy of the reference under baseline/_ref, `kind: reference`) or the
                numpy port in oracle/ (`kind: port`) on the host cores, bounded sample, multiprocessing over tracks
 
@@ -462,8 +463,9 @@ def run_ours(args):
 
     # ---------------- N > 1: host link probe and BASELINE config 4 (long signal, halo + all-gather)
     host_link = long_signal = None
-    if world > 1:
+    if not args.no_e2e:
         host_link = probe_host_link(torch, dev, barrier, max_over_ranks, sum_over_ranks)
+    if world > 1:
         try:
             long_signal = run_long_signal(torch, dist, dev, local, world, rank, barrier, max_over_ranks)
         except Exception as exc:                                                 # never lose the headline line
@@ -534,6 +536,11 @@ def run_ours(args):
         line["configs"] = configs
     if host_link is not None:
         line["host_link"] = host_link
+        for key in ("e2e", "e2e_program"):                  # how much of the measured link the host path uses
+            blk = line.get(key)
+            if isinstance(blk, dict) and blk.get("ms_per_step") and host_link.get("h2d_gbs"):
+                blk["h2d_gbs"] = blk["h2d_bytes_per_step"] * world / (blk["ms_per_step"] * 1e-3) / 1e9
+                blk["link_frac"] = blk["h2d_gbs"] / host_link["h2d_gbs"]
     if long_signal is not None:
         line["long_signal"] = long_signal
     print(json.dumps(line))

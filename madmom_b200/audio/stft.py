@@ -135,6 +135,10 @@ class ShortTimeFourierTransform(DeviceResult):
         self.frames = frames
         self.window = window
         self.fft_window = chain.resolved_fft_window()
+        if window is None and fft_window is None and not np.issubdtype(frames.signal.dtype, np.integer):
+            # stft.py:331-350: no window and no integer range to scale by -> the attribute is None (the kernel still
+            # multiplies by the ones the chain resolved)
+            self.fft_window = None
         self.fft_size = frame_size
         self.circular_shift = bool(circular_shift)
         self.include_nyquist = bool(include_nyquist)

@@ -213,6 +213,39 @@ def test_float_signal_window_none(sample_pcm):
     assert np.abs(got - ref).max() <= 2e-6 * np.abs(ref).max()
 
 
+def test_stft_attributes_and_scaled_signal(sig, sample_pcm):
+    """The reference's own assertions on ShortTimeFourierTransform (tests/test_audio_stft.py:168-217): attribute
+    values, STFT of an STFT, an int16 signal against the same signal scaled to -1..1 (the window takes the 1 / 32767),
+    window=None, include_nyquist."""
+    from madmom_b200.audio.signal import Signal
+    from madmom_b200.audio.stft import ShortTimeFourierTransform, fft_frequencies
+    from madmom_b200.audio.spectrogram import Spectrogram
+    from madmom_b200.audio.stft import Phase
+    result = ShortTimeFourierTransform(sig)
+    assert result.shape == (281, 1024) and result.fft_size == 2048
+    assert result.circular_shift is False and result.include_nyquist is False
+    assert np.allclose(result.window, np.hanning(2048))
+    assert np.allclose(result.fft_window, np.hanning(2048) / 32767)
+    assert np.allclose(result.bin_frequencies, fft_frequencies(1024, 44100))
+    assert result.num_frames == 281 and result.num_bins == 1024
+    assert np.allclose(np.asarray(ShortTimeFourierTransform(result)), np.asarray(result))     # from STFT
+    assert isinstance(result.spec(), Spectrogram) and isinstance(result.phase(), Phase)
+    # test_fft_window: both STFTs must be the same
+    scaling = float(np.iinfo(sample_pcm.dtype).max)
+    scaled = Signal((sample_pcm / scaling).astype(np.float32), sample_rate=44100)
+    scaled_result = ShortTimeFourierTransform(scaled)
+    assert np.allclose(np.asarray(result), np.asarray(scaled_result), atol=1e-6)
+    plain = ShortTimeFourierTransform(sig, window=None)
+    assert np.allclose(plain.fft_window, np.ones(2048, dtype=float) / scaling)
+    assert ShortTimeFourierTransform(scaled, window=None).fft_window is None
+    assert np.allclose(np.asarray(plain), np.asarray(ShortTimeFourierTransform(scaled, window=None)), atol=2e-5)
+    # test_nyquist
+    nyq = ShortTimeFourierTransform(sig, include_nyquist=True)
+    assert nyq.shape == (281, 1025) and nyq.fft_size == 2048 and nyq.include_nyquist is True
+    assert np.allclose(nyq.bin_frequencies, fft_frequencies(1025, 44100))
+    assert np.array_equal(np.asarray(nyq)[:, :1024], np.asarray(result))
+
+
 def test_mel_filterbank_and_cnn_front_end(sig, ref_mel):
     """SURVEY 8(f) row 2 against vectors of the real reference (tests/golden/make_golden_mel.py):
     FilteredSpectrogram(MelFilterbank, 40) with the literals of tests/test_audio_spectrogram.py:173-180, a

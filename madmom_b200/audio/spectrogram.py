@@ -35,12 +35,21 @@ POSITIVE_DIFFS = False
 
 
 class Spectrogram(DeviceResult):
-    """Magnitude spectrogram |STFT|, (num_frames, num_bins) float32."""
+    """Magnitude spectrogram |STFT|, (num_frames, num_bins) float32.
+
+    `_generic`: the fused kernel computes the stages in the reference's canonical order (filter, logarithm,
+    difference).  The reference's classes also accept any other order -- `LogarithmicSpectrogram(...).filter()`,
+    the logarithm of a logarithm, the difference of a difference (tests/test_audio_spectrogram.py:321-324) -- and
+    just apply `np.dot` / `log` / the lagged difference to whatever matrix they are given.  Such results are marked
+    generic: they are computed from their source's device matrix (a plain float32 matrix product, an element-wise
+    logarithm, `mmb_matrix_diff`), off the fused path, and everything built on them stays generic."""
     _output = "spec"
+    _generic = False
 
     def __init__(self, stft, **kwargs):
         self._source = None
         if isinstance(stft, Spectrogram):
+            self._generic = stft._generic
             # already a Spectrogram (of any stage): the reference keeps the given data and only re-types it
             # (madmom/audio/spectrogram.py:125-127), so a filtered / logarithmic / difference matrix stays what it is
             DeviceResult.__init__(self, stft._chain.copy())
@@ -104,10 +113,8 @@ class FilteredSpectrogram(Spectrogram):
         if not isinstance(spectrogram, Spectrogram):
             spectrogram = Spectrogram(spectrogram, **kwargs)
         c0 = spectrogram._chain
-        if (isinstance(spectrogram, (FilteredSpectrogram, LogarithmicSpectrogram, SpectrogramDifference)) or
-                c0.filterbank is not None or c0.log_mode != 0 or c0.diff_frames != 0):
-            raise NotImplementedError("filtering an already filtered / logarithmic spectrogram is not available "
-                                      "on the GPU path")
+        generic = (spectrogram._generic or c0.filterbank is not None or c0.log_mode != 0 or c0.diff_frames != 0 or
+                   isinstance(spectrogram, (FilteredSpectrogram, LogarithmicSpectrogram, SpectrogramDifference)))
         if isinstance(filterbank, type) and issubclass(filterbank, Filterbank):
             fb_kw = dict(num_bands=num_bands, fmin=fmin, fmax=fmax, norm_filters=norm_filters,
                          unique_filters=unique_filters)
@@ -120,13 +127,26 @@ class FilteredSpectrogram(Spectrogram):
             raise ValueError("filterbank has %d bins, the spectrogram %d" % (filterbank.shape[0],
                                                                            spectrogram.num_bins))
         DeviceResult.__init__(self, spectrogram._chain.copy())
-        self._chain.filterbank = filterbank
+        self._generic = generic
+        self._filter_source = spectrogram if generic else None
+        if not generic:
+            self._chain.filterbank = filterbank
         self.filterbank = filterbank
         self.stft = spectrogram.stft
         self.frames = spectrogram.frames
 
+    def _compute(self):
+        if self._generic:
+            # np.dot(spectrogram, filterbank) (madmom/audio/spectrogram.py:382) on the device, float32 like there
+            import torch
+            x = self._filter_source.tensor
+            w = torch.from_numpy(np.ascontiguousarray(np.asarray(self.filterbank), dtype=np.float32)).to(x.device)
+            return torch.matmul(x, w)
+        return Spectrogram._compute(self)
+
     def _shape(self):
-        return self.stft.num_frames, self.filterbank.shape[1]
+        rows = self._filter_source.shape[0] if self._generic else self.stft.num_frames
+        return rows, self.filterbank.shape[1]
 
     @property
     def bin_frequencies(self):
@@ -163,15 +183,17 @@ class LogarithmicSpectrogram(Spectrogram):
     def __init__(self, spectrogram, log=LOG, mul=MUL, add=ADD, **kwargs):
         if not isinstance(spectrogram, Spectrogram):
             spectrogram = Spectrogram(spectrogram, **kwargs)
-        if (isinstance(spectrogram, (LogarithmicSpectrogram, SpectrogramDifference)) or
-                spectrogram._chain.log_mode != 0 or spectrogram._chain.diff_frames != 0):
-            raise NotImplementedError("the logarithm of an already logarithmic spectrogram / a difference is not "
-                                      "available on the GPU path")
+        generic = (spectrogram._generic or spectrogram._chain.log_mode != 0 or spectrogram._chain.diff_frames != 0 or
+                   isinstance(spectrogram, (LogarithmicSpectrogram, SpectrogramDifference)))
         DeviceResult.__init__(self, spectrogram._chain.copy())
+        self._generic = generic
+        self._log = log
         c = self._chain
-        c.log_mode = _engine.log_mode_of(log, mul, add)
-        c.mul = 1.0 if mul is None else float(mul)
-        c.add = 0.0 if add is None else float(add)
+        mode = _engine.log_mode_of(log, mul, add)            # raises for a logarithm the kernels do not have
+        if not generic:
+            c.log_mode = mode
+            c.mul = 1.0 if mul is None else float(mul)
+            c.add = 0.0 if add is None else float(add)
         # an unfiltered spectrogram is scaled in the magnitude epilogue of the kernel ('spec' output)
         self._output = "log" if c.filterbank is not None else "spec"
         self.mul = mul
@@ -179,6 +201,20 @@ class LogarithmicSpectrogram(Spectrogram):
         self.stft = spectrogram.stft
         self.frames = spectrogram.frames
         self.spectrogram = spectrogram
+
+    def _compute(self):
+        if self._generic:
+            # log(mul * x + add) in float32, in that order (madmom/audio/spectrogram.py:537-544)
+            import torch
+            x = self.spectrogram.tensor
+            if self.mul is not None:
+                x = x * float(self.mul)
+            if self.add is not None:
+                x = x + float(self.add)
+            if self._log is None:
+                return x
+            return {np.log10: torch.log10, np.log: torch.log, np.log2: torch.log2}[self._log](x)
+        return Spectrogram._compute(self)
 
     def _shape(self):
         return self.spectrogram.shape
@@ -259,8 +295,8 @@ class SpectrogramDifference(Spectrogram):
                  positive_diffs=POSITIVE_DIFFS, keep_dims=True, **kwargs):
         if not isinstance(spectrogram, Spectrogram):
             spectrogram = Spectrogram(spectrogram, **kwargs)
-        if isinstance(spectrogram, SpectrogramDifference) or spectrogram._chain.diff_frames != 0:
-            raise NotImplementedError("the difference of a difference is not available on the GPU path")
+        generic = (spectrogram._generic or isinstance(spectrogram, SpectrogramDifference) or
+                   spectrogram._chain.diff_frames != 0)
         if diff_frames is None:
             diff_frames = _diff_frames(diff_ratio, hop_size=spectrogram.stft.frames.hop_size,
                                        frame_size=spectrogram.stft.frames.frame_size,
@@ -269,6 +305,7 @@ class SpectrogramDifference(Spectrogram):
         if diff_frames < 1:
             raise ValueError("number of `diff_frames` must be >= 1")
         DeviceResult.__init__(self, spectrogram._chain.copy())
+        self._generic = generic
         c = self._chain
         c.diff_frames = diff_frames
         c.diff_max_bins = int(diff_max_bins) if diff_max_bins is not None and diff_max_bins > 1 else 0
@@ -284,9 +321,9 @@ class SpectrogramDifference(Spectrogram):
 
     @property
     def _fused(self):
-        # unfiltered spectrograms (1024+ columns) do not fit the fused kernel's shared-memory ring: they are
-        # materialised and differenced by mmb_matrix_diff
-        return self._chain.filterbank is not None
+        # unfiltered spectrograms (1024+ columns) do not fit the fused kernel's shared-memory ring, and generic
+        # sources are not described by the chain: both are materialised and differenced by mmb_matrix_diff
+        return self._chain.filterbank is not None and not self._generic
 
     def _run(self, want_diff, want_odf):
         if self._fused:

@@ -70,8 +70,9 @@ def complex_flux(spectrogram, diff_frames=None, diff_max_bins=3, temporal_filter
         raise NotImplementedError("temporal_origin != 0 is not available on the GPU path")
     if temporal_filter > 1 and temporal_filter % 2 == 0:
         raise NotImplementedError("even temporal_filter sizes are not available on the GPU path")
-    if spectrogram._chain.filterbank is None:
-        raise NotImplementedError("complex_flux of an unfiltered spectrogram is not available on the GPU path")
+    if spectrogram._chain.filterbank is None or getattr(spectrogram, "_generic", False):
+        raise NotImplementedError("complex_flux needs a filtered (optionally logarithmic) spectrogram in the "
+                                  "reference's canonical order on the GPU path")
     if spectrogram.stft.fft_size != 2048:
         raise NotImplementedError("complex_flux is implemented for frame_size 2048 only")
     diff = SpectrogramDifference(spectrogram, diff_frames=diff_frames, diff_max_bins=diff_max_bins,

@@ -56,6 +56,11 @@ def ref_phase():
 
 
 @pytest.fixture(scope="session")
+def ref_acts():
+    return _npz("ref_acts.npz")
+
+
+@pytest.fixture(scope="session")
 def ref_odfs():
     return _npz("ref_odfs.npz")
 

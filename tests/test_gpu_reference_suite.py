@@ -285,3 +285,93 @@ def test_stages_in_any_order(sig):
     assert np.allclose(np.asarray(Spectrogram(filt_of_log)), want, rtol=1e-5, atol=1e-6)     # re-typing keeps it
     with pytest.raises(NotImplementedError):
         complex_flux(filt_of_log)
+
+
+def test_peak_picking_and_processor_classes(ref_acts):
+    """TestPeakPickingFunction.test_online and TestOnsetPeakPickingProcessorClass (tests/test_features_onsets.py:
+    247-297) on the reference's own activation fixtures; integers and onset times equal the real reference's
+    (tests/golden/make_golden_acts.py).  Online (frame-by-frame) mode is out of scope and says so."""
+    from madmom_b200.features.onsets import peak_picking, OnsetPeakPickingProcessor
+    act, fps = ref_acts["rnn_act"], float(ref_acts["rnn_fps"])
+    onsets = peak_picking(act, threshold=0.23, post_max=0)
+    assert list(onsets) == [1, 3, 10, 12, 29, 46, 62, 63, 77, 79, 81, 99, 100, 113, 115, 148, 149, 164, 181, 183,
+                            216, 234, 250, 268] and len(onsets) == 24
+    assert np.array_equal(onsets, ref_acts["rnn_peaks_online_params"])
+    sf, sf_fps = ref_acts["sf_act"], float(ref_acts["sf_fps"])
+    proc = OnsetPeakPickingProcessor(threshold=1.1, pre_max=0.01, post_max=0.05, pre_avg=0.15, post_avg=0,
+                                     combine=0.03, delay=0, fps=sf_fps)
+    got = proc(sf)
+    assert np.allclose(got, [0.01, 0.085, 0.275, 0.445, 0.61, 0.795, 0.98, 1.115, 1.365, 1.475, 1.62, 1.795, 2.14,
+                             2.33, 2.485, 2.665])
+    assert np.array_equal(got, ref_acts["sf_onsets"])
+    proc.delay = 1                                                                       # test_delay
+    assert np.allclose(proc(sf) - 1, ref_acts["sf_onsets"]) and np.array_equal(proc(sf), ref_acts["sf_onsets_delay1"])
+    with pytest.raises(NotImplementedError):
+        OnsetPeakPickingProcessor(threshold=0.23, online=True, fps=fps)
+    # what the online processor returns for the whole activation is what the offline one returns with the
+    # parameters online mode forces (smooth = post_avg = post_max = 0)
+    off = OnsetPeakPickingProcessor(threshold=0.23, smooth=0, post_avg=0, post_max=0, fps=fps)(act)
+    assert np.array_equal(off, ref_acts["rnn_onsets_online"])
+    for combine in (0.0, 0.03, 0.1):
+        p = OnsetPeakPickingProcessor(threshold=0.02, smooth=0.02, pre_avg=0.1, post_avg=0.05, pre_max=0.02,
+                                      post_max=0.03, combine=combine, delay=0.005, fps=fps)
+        assert np.array_equal(p(act), ref_acts["rnn_onsets_combine_%g" % combine]), combine
+
+
+def test_spectral_onset_processor_class(sig):
+    """TestSpectralOnsetProcessorClass, tests/test_features_onsets.py:155-207: which processors the chain is made of
+    for every option, the unknown method, the literal values of the default chain."""
+    from madmom_b200.audio.signal import SignalProcessor, FramedSignalProcessor
+    from madmom_b200.audio.stft import ShortTimeFourierTransformProcessor
+    from madmom_b200.audio.filters import LogarithmicFilterbank
+    from madmom_b200.audio.spectrogram import (SpectrogramProcessor, FilteredSpectrogramProcessor,
+                                               LogarithmicSpectrogramProcessor)
+    from madmom_b200.features.onsets import SpectralOnsetProcessor, spectral_flux, phase_deviation
+    proc = SpectralOnsetProcessor()
+    assert isinstance(proc.processors[0], SignalProcessor) and isinstance(proc.processors[1], FramedSignalProcessor)
+    assert isinstance(proc.processors[2], ShortTimeFourierTransformProcessor)
+    assert isinstance(proc.processors[3], SpectrogramProcessor) and proc.processors[4] == spectral_flux
+    proc = SpectralOnsetProcessor(filterbank=LogarithmicFilterbank)
+    assert isinstance(proc.processors[4], FilteredSpectrogramProcessor) and proc.processors[5] == spectral_flux
+    proc = SpectralOnsetProcessor(log=np.log10)
+    assert isinstance(proc.processors[4], LogarithmicSpectrogramProcessor) and proc.processors[5] == spectral_flux
+    proc = SpectralOnsetProcessor(filterbank=LogarithmicFilterbank, log=np.log10)
+    assert isinstance(proc.processors[4], FilteredSpectrogramProcessor)
+    assert isinstance(proc.processors[5], LogarithmicSpectrogramProcessor) and proc.processors[6] == spectral_flux
+    proc = SpectralOnsetProcessor(onset_method="phase_deviation")
+    assert isinstance(proc.processors[2], ShortTimeFourierTransformProcessor)
+    assert proc.processors[2].circular_shift and proc.processors[4] == phase_deviation
+    with pytest.raises(ValueError):
+        SpectralOnsetProcessor(onset_method="nonexistent")
+    odf = SpectralOnsetProcessor()(sig)
+    assert np.allclose(odf[:6], [0., 100.90120697, 74.44419861, 40.277565, 57.95736313, 46.15561295])
+
+
+def test_onset_functions_on_the_reference_inputs(sig):
+    """The function tests of tests/test_features_onsets.py:35-152 on the same two inputs (:25-27): a circularly
+    shifted Spectrogram and LogarithmicFilteredSpectrogram(num_bands=24, mul=1, add=1) of it; literals within
+    the stated bound 1e-5 + 1e-4 |ref|, ValueError where the reference raises it."""
+    from madmom_b200.audio.spectrogram import Spectrogram, LogarithmicFilteredSpectrogram
+    from madmom_b200.features import onsets as ON
+    sample_spec = Spectrogram(sig, circular_shift=True)
+    lfs = LogarithmicFilteredSpectrogram(sample_spec, num_bands=24, mul=1, add=1)
+    for fn, arg, want in (
+            (ON.high_frequency_content, lfs, [8.97001563, 9.36399107, 8.64144536, 8.34977449, 8.21097918, 8.40412515]),
+            (ON.spectral_diff, lfs, [0, 0.55715936, 0.64004618, 0.0810971, 0.295396, 0.16324584]),
+            (ON.spectral_flux, lfs, [0, 3.91207361, 2.91675663, 1.38361311, 2.59582925, 2.16986609]),
+            (ON.superflux, lfs, [0, 2.08680153, 0.6411702, 0.38634294, 0.40202433, 0.63349575]),
+            (ON.complex_flux, lfs, [0, 0.476213485, 0.0877621323, 0.0593151376, 0.0654867291, 0.0954693183]),
+            (ON.modified_kullback_leibler, lfs, [0, 0.71910584, 0.6664055, 0.68092251, 0.69984031, 0.71744561]),
+            (ON.phase_deviation, lfs, [0, 0, 0.71957183, 0.91994524, 0.9418999, 0.86083585]),
+            (ON.weighted_phase_deviation, sample_spec, [0, 0, 0.19568817, 0.20483065, 0.17890805, 0.16970603]),
+            (ON.normalized_weighted_phase_deviation, sample_spec,
+             [0, 0, 0.46018526, 0.50193471, 0.42031503, 0.40806249]),
+            (ON.complex_domain, sample_spec,
+             [399.29980469, 585.9564209, 262.08010864, 225.84718323, 196.88954163, 200.32469177]),
+            (ON.rectified_complex_domain, sample_spec, [0, 394.165222, 119.79425, 96.70564, 122.52311, 92.61698])):
+        got = np.asarray(fn(arg))[:6]
+        assert np.allclose(got, want, rtol=1e-4, atol=1e-5), (fn.__name__, got, want)
+    for fn in (ON.weighted_phase_deviation, ON.normalized_weighted_phase_deviation, ON.complex_domain,
+               ON.rectified_complex_domain):
+        with pytest.raises(ValueError):
+            fn(lfs)

@@ -404,3 +404,30 @@ def test_phase_and_local_group_delay_vs_reference(ref_phase):
     assert np.allclose(O.local_group_delay(np.arange(20).reshape(10, 2) * 2), np.tile([-2, 0], 10).reshape(10, 2))
     assert np.allclose(O.local_group_delay(np.arange(20).reshape(10, 2) * 4),
                        np.tile([2.28318531, 0], 10).reshape(10, 2))
+
+
+def test_peak_picking_rnn_fixture(ref_acts):
+    """The oracle's peak picking against the real reference on its sample.onsets_rnn.npz fixture
+    (tests/golden/make_golden_acts.py) and against the literals of tests/test_features_onsets.py:247-269."""
+    act, fps = ref_acts["rnn_act"], float(ref_acts["rnn_fps"])
+    peaks = O.peak_picking(act, 0.23, post_max=0)
+    assert np.array_equal(peaks, ref_acts["rnn_peaks_online_params"])
+    assert list(peaks) == [1, 3, 10, 12, 29, 46, 62, 63, 77, 79, 81, 99, 100, 113, 115, 148, 149, 164, 181, 183, 216,
+                           234, 250, 268]
+    sf, sf_fps = ref_acts["sf_act"], float(ref_acts["sf_fps"])
+    kw = dict(threshold=1.1, pre_max=0.01, post_max=0.05, pre_avg=0.15, post_avg=0, combine=0.03)
+    got = O.onset_peak_picking(sf, sf_fps, delay=0, **kw)
+    assert np.array_equal(got, ref_acts["sf_onsets"])
+    assert np.allclose(got, [0.01, 0.085, 0.275, 0.445, 0.61, 0.795, 0.98, 1.115, 1.365, 1.475, 1.62, 1.795, 2.14,
+                             2.33, 2.485, 2.665])
+    assert np.array_equal(O.onset_peak_picking(sf, sf_fps, delay=1, **kw), ref_acts["sf_onsets_delay1"])
+    # the online processor fed everything at once equals the offline one with the parameters it ends up with
+    off = O.onset_peak_picking(act, fps, threshold=0.23, smooth=0, post_avg=0, post_max=0)
+    assert np.array_equal(off, ref_acts["rnn_onsets_offline_same_params"])
+    assert np.array_equal(off, ref_acts["rnn_onsets_online"])
+    assert np.allclose(off, [0.01, 0.1, 0.29, 0.46, 0.62, 0.77, 0.81, 0.99, 1.13, 1.48, 1.64, 1.81, 2.16, 2.34, 2.5,
+                             2.68])
+    for combine in (0.0, 0.03, 0.1):
+        got = O.onset_peak_picking(act, fps, threshold=0.02, smooth=0.02, pre_avg=0.1, post_avg=0.05, pre_max=0.02,
+                                   post_max=0.03, combine=combine, delay=0.005)
+        assert np.array_equal(got, ref_acts["rnn_onsets_combine_%g" % combine]), combine

@@ -286,3 +286,51 @@ def test_window_cache_and_plan_key():
         fb[0, 0] = 1.0                      # frozen: a changed filterbank cannot run with the old plan
     same = LogarithmicFilterbank(R.fft_frequencies(1024, 44100), num_bands=24, norm_filters=False)
     assert _filterbank_key(same) == k1      # equal weights, another object: same plan
+
+
+def test_framed_signal_like_the_reference_tests(sample_pcm):
+    """The reference's FramedSignal assertions, tests/test_audio_signal.py:1144-1307 (small arrays, `end`, slicing,
+    the origin literals, fps), on the drop-in class."""
+    from madmom_b200.audio.signal import Signal, FramedSignal
+    result = FramedSignal(np.arange(10), 4, 2)
+    assert np.allclose(result[0], [0, 0, 0, 1])
+    assert result.frame_size == 4 and result.hop_size == 2. and result.origin == 0 and result.num_frames == 5
+    assert len(result) == 5 and result.frame_rate is None and result.fps is None
+    assert result.overlap_factor == 0.5 and result.shape == (5, 4) and result.ndim == 2
+    assert FramedSignal(np.arange(10), 4, 2, end="extend").num_frames == 6
+    result = FramedSignal(np.arange(10), 4, 2, sample_rate=4)
+    for i, want in enumerate(([0, 0, 0, 1], [0, 1, 2, 3], [2, 3, 4, 5], [4, 5, 6, 7], [6, 7, 8, 9])):
+        assert np.allclose(result[i], want)
+    assert np.allclose(result[-1], [6, 7, 8, 9])
+    with pytest.raises(IndexError):
+        result[5]
+    assert result.frame_rate == 2 and result.fps == 2 and len(result) == 5
+    sl = result[1:]                                                         # test_values_slicing
+    assert np.allclose(sl[0], [0, 1, 2, 3]) and np.allclose(sl[-2], [4, 5, 6, 7]) and np.allclose(sl[3], [6, 7, 8, 9])
+    with pytest.raises(IndexError):
+        sl[4]
+    assert sl.frame_size == 4 and sl.hop_size == 2. and sl.origin == -2 and sl.num_frames == 4
+    assert len(sl) == 4 and sl.shape == (4, 4) and sl.fps == 2 and sl.overlap_factor == 0.5
+    sl = result[2:4]
+    assert sl.shape == (2, 4) and np.allclose(sl[0], [2, 3, 4, 5]) and np.allclose(sl[1], [4, 5, 6, 7])
+    with pytest.raises(IndexError):
+        sl[2]
+    with pytest.raises(ValueError):
+        result[2:4:2]
+    with pytest.raises(TypeError):
+        result["foo":"bar"]
+    with pytest.raises(TypeError):
+        result["bar"]
+    sig = Signal(sample_pcm, sample_rate=44100)                             # test_values_file and the origins
+    frames = FramedSignal(sig)
+    assert np.allclose(frames[0][:5], [0, 0, 0, 0, 0]) and np.allclose(frames[3], sample_pcm[299: 299 + 2048])
+    assert frames.overlap_factor == 0.78466796875 and frames.frame_rate == 100.
+    online = FramedSignal(sig, origin="online")
+    assert online.origin == 1023 and online.num_frames == 281
+    assert np.allclose(online[6], sample_pcm[599: 599 + 2048])
+    for literal, want in (("left", 1023), (10, 10), ("offline", 0), ("center", 0), ("right", -1024),
+                          ("future", -1024), (-10, -10)):
+        assert FramedSignal(sig, origin=literal).origin == want, literal
+    shifted = FramedSignal(sig, origin=-10)
+    assert shifted.num_frames == 281 and np.allclose(shifted[3], sample_pcm[309: 309 + 2048])
+    assert FramedSignal(sig, fps=200).hop_size == 220.5 and FramedSignal(sig, fps=50).hop_size == 882.

@@ -334,3 +334,53 @@ def test_framed_signal_like_the_reference_tests(sample_pcm):
     shifted = FramedSignal(sig, origin=-10)
     assert shifted.num_frames == 281 and np.allclose(shifted[3], sample_pcm[309: 309 + 2048])
     assert FramedSignal(sig, fps=200).hop_size == 220.5 and FramedSignal(sig, fps=50).hop_size == 882.
+
+
+def test_signal_frame_and_signal_processor_like_the_reference_tests(sample_pcm, tmp_path):
+    """tests/test_audio_signal.py:796-995 on the drop-in `signal_frame` and `SignalProcessor`: frames of short,
+    stereo and shifted inputs, a fractional frame size, the processor's defaults, the literal samples after
+    normalisation and after -10 dB (int16 truncation), dump / load."""
+    from madmom_b200.audio.signal import Signal, SignalProcessor, signal_frame
+    from madmom_b200.processors import Processor
+    assert signal_frame(np.arange(10), 0, 4, 2).dtype == int
+    assert signal_frame(np.arange(10, dtype=float), 0, 4, 2).dtype == float
+    sig = Signal(sample_pcm, sample_rate=44100)
+    for args in ((0, 4, 2), (2000, 400, 200), (-10, 400, 200)):
+        assert np.asarray(signal_frame(sig, *args)).dtype == np.int16
+    for idx, want in ((0, [0, 0, 0, 0, 0, 0, 1, 2, 3, 0]), (1, [0, 1, 2, 3, 0, 0, 0, 0, 0, 0]), (2, [0] * 10),
+                      (-2, [0] * 10)):
+        assert np.allclose(signal_frame(np.arange(4), idx, 10, 5), want)                 # test_short_input_length
+    for idx, want in ((-1, [0, 0, 0, 0]), (0, [0, 0, 0, 1]), (1, [0, 1, 2, 3]), (2, [2, 3, 4, 5]), (3, [4, 5, 6, 7]),
+                      (4, [6, 7, 8, 9]), (5, [8, 9, 0, 0])):
+        assert np.allclose(signal_frame(np.arange(10), idx, 4, 2), want)                 # test_values
+    stereo = np.tile(np.arange(10)[:, np.newaxis], 2)
+    for idx, want in ((0, [0, 0, 0, 1]), (1, [0, 1, 2, 3]), (5, [8, 9, 0, 0]), (6, [0, 0, 0, 0])):
+        assert np.allclose(signal_frame(stereo, idx, 4, 2), np.tile(np.array(want)[:, None], 2))
+    for idx, want in ((0, [0, 0, 1]), (1, [1, 2, 3]), (2, [3, 4, 5])):
+        assert np.allclose(signal_frame(np.arange(10), idx, 3.5, 2), want)               # test_float_hop_size
+    for origin, want in ((1, [0, 0, 0, 0]), (-1, [0, 0, 1, 2]), (-2, [0, 1, 2, 3]), (-4, [2, 3, 4, 5])):
+        assert np.allclose(signal_frame(np.arange(10), 0, 4, 2, origin), want)           # test_origin
+    assert np.allclose(signal_frame(np.arange(10), 0, 5, 2, -2.5), [0, 1, 2, 3, 4])
+    proc = SignalProcessor()
+    assert isinstance(proc, Processor)
+    assert proc.sample_rate is None and proc.num_channels is None and proc.start is None and proc.stop is None
+    assert proc.norm is False and isinstance(proc.gain, float) and proc.gain == 0
+    result = proc.process(sig)
+    assert isinstance(result, Signal) and isinstance(result, np.ndarray) and result.dtype == np.int16
+    assert np.allclose(result[:5], [-2494, -2510, -2484, -2678, -2833]) and len(result) == 123481
+    assert result.min() == -20603 and result.max() == 17977 and result.mean() == -172.88385257650975
+    assert result.sample_rate == 44100 and result.num_samples == 123481 and result.num_channels == 1
+    proc.norm = True                                                                      # test_process_norm
+    result = proc.process(sig)
+    assert result.dtype == np.int16 and np.allclose(result[:5], [-3966, -3991, -3950, -4259, -4505])
+    assert result.min() == -32767 and result.max() == 28590 and result.mean() == -274.92599671204476
+    proc.norm, proc.gain = False, -10                                                     # test_process_gain
+    result = proc.process(sig)
+    assert result.dtype == np.int16 and np.allclose(result[:5], [-788, -793, -785, -846, -895])
+    assert len(result) == 123481 and result.sample_rate == 44100
+    proc = SignalProcessor()
+    proc.dump(str(tmp_path / "signal_processor.pkl"))                                     # test_pickle
+    back = SignalProcessor.load(str(tmp_path / "signal_processor.pkl"))
+    assert type(back) is SignalProcessor
+    for name in ("sample_rate", "num_channels", "start", "stop", "norm", "gain"):
+        assert getattr(back, name) == getattr(proc, name)

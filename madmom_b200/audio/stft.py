@@ -227,6 +227,14 @@ class Phase(DeviceResult):
     def bin_frequencies(self):
         return self.stft.bin_frequencies
 
+    @property
+    def num_frames(self):
+        return int(self.shape[0])
+
+    @property
+    def num_bins(self):
+        return int(self.shape[1])
+
     def local_group_delay(self, **kwargs):
         return LocalGroupDelay(self, **kwargs)
 
@@ -259,6 +267,14 @@ class LocalGroupDelay(DeviceResult):
     @property
     def bin_frequencies(self):
         return self.stft.bin_frequencies
+
+    @property
+    def num_frames(self):
+        return int(self.shape[0])
+
+    @property
+    def num_bins(self):
+        return int(self.shape[1])
 
 
 LGD = LocalGroupDelay

@@ -375,3 +375,35 @@ def test_onset_functions_on_the_reference_inputs(sig):
                ON.rectified_complex_domain):
         with pytest.raises(ValueError):
             fn(lfs)
+
+
+def test_stft_processor_phase_and_lgd_classes(sig):
+    """ShortTimeFourierTransformProcessorClass, PhaseClass, LocalGroupDelayClass, tests/test_audio_stft.py:218-320."""
+    from madmom_b200.audio.stft import (ShortTimeFourierTransform, ShortTimeFourierTransformProcessor, Phase,
+                                        LocalGroupDelay, STFT, fft_frequencies)
+    proc = ShortTimeFourierTransformProcessor()
+    assert proc.window == np.hanning and proc.fft_size is None and proc.circular_shift is False
+    result = proc.process(sig)
+    assert isinstance(result, ShortTimeFourierTransform) and result.shape == (281, 1024)
+    assert np.allclose(result.bin_frequencies, fft_frequencies(1024, 44100)) and result.fft_size == 2048
+    assert np.allclose(result.fft_window, np.hanning(2048) / 32767)
+    assert result.num_bins == 1024 and result.num_frames == 281
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")                    # from a signal the STFT is circularly shifted: no warning
+        phase = Phase(sig)
+        lgd = LocalGroupDelay(sig)
+    assert phase.stft.circular_shift is True
+    assert isinstance(phase, Phase) and isinstance(phase.stft, ShortTimeFourierTransform)
+    assert isinstance(phase.bin_frequencies, np.ndarray)
+    assert isinstance(phase.num_bins, int) and isinstance(phase.num_frames, int)
+    assert phase.shape == (281, 1024) and np.allclose(phase.bin_frequencies, fft_frequencies(1024, 44100))
+    assert phase.num_bins == 1024 and phase.num_frames == 281
+    assert isinstance(phase.local_group_delay(), LocalGroupDelay) and isinstance(phase.lgd(), LocalGroupDelay)
+    with pytest.warns(RuntimeWarning):
+        Phase(STFT(sig))
+    assert isinstance(lgd, LocalGroupDelay) and isinstance(lgd.phase, Phase)
+    assert isinstance(lgd.stft, ShortTimeFourierTransform) and isinstance(lgd.bin_frequencies, np.ndarray)
+    assert isinstance(lgd.num_bins, int) and isinstance(lgd.num_frames, int)
+    assert lgd.shape == (281, 1024) and np.allclose(lgd.bin_frequencies, fft_frequencies(1024, 44100))
+    assert lgd.num_bins == 1024 and lgd.num_frames == 281

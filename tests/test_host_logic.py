@@ -384,3 +384,44 @@ def test_signal_frame_and_signal_processor_like_the_reference_tests(sample_pcm, 
     assert type(back) is SignalProcessor
     for name in ("sample_rate", "num_channels", "start", "stop", "norm", "gain"):
         assert getattr(back, name) == getattr(proc, name)
+
+
+def test_framed_signal_processor_like_the_reference_tests(sample_pcm, tmp_path):
+    """tests/test_audio_signal.py:1338-1440 on the drop-in FramedSignalProcessor: defaults, `origin='online'`, fps,
+    `end`, the wrong `end`, dump / load."""
+    from madmom_b200.audio.signal import Signal, FramedSignal, FramedSignalProcessor
+    from madmom_b200.processors import Processor
+    sig = Signal(sample_pcm, sample_rate=44100)
+    proc = FramedSignalProcessor()
+    assert isinstance(proc, Processor) and isinstance(proc.process(sig), FramedSignal)
+    assert proc.frame_size == 2048 and proc.hop_size == 441. and proc.fps is None and proc.origin == 0
+    assert proc.end == "normal" and proc.num_frames is None
+    result = proc.process(sig)
+    assert np.allclose(result[0][:1023], np.zeros(1023)) and np.allclose(result[0][1024], -2494)
+    assert result.frame_size == 2048 and result.hop_size == 441. and result.origin == 0 and result.num_frames == 281
+    assert len(result) == 281 and result.fps == 100. and result.frame_rate == 100.
+    assert result.overlap_factor == 0.78466796875 and result.shape == (281, 2048) and result.ndim == 2
+    proc.end = "bogus"
+    assert proc.end == "bogus"
+    proc.end = "normal"
+    proc.origin = "online"                                                    # test_process_online
+    result = proc.process(sig)
+    assert np.allclose(result[0][-1], -2494) and len(result) == 281 and result.num_frames == 281
+    proc.origin = 0
+    proc.fps = 200.                                                           # test_process_fps
+    result = proc.process(sig)
+    assert np.allclose(result[0][:1023], np.zeros(1023)) and np.allclose(result[0][1024], -2494)
+    assert len(result) == 561 and result.num_frames == 561
+    proc.fps = None
+    proc.frame_size, proc.hop_size = 10, 6                                    # test_process_end
+    assert proc.process(np.arange(18)).num_frames == 3
+    proc.end = "extend"
+    assert len(proc.process(np.arange(18))) == 4
+    with pytest.raises(ValueError):
+        FramedSignalProcessor(end="bla").process(sig)
+    proc = FramedSignalProcessor()
+    proc.dump(str(tmp_path / "framed.pkl"))
+    back = FramedSignalProcessor.load(str(tmp_path / "framed.pkl"))
+    assert type(back) is FramedSignalProcessor
+    for name in ("frame_size", "hop_size", "fps", "end"):
+        assert getattr(back, name) == getattr(proc, name)

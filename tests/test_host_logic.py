@@ -425,3 +425,75 @@ def test_framed_signal_processor_like_the_reference_tests(sample_pcm, tmp_path):
     assert type(back) is FramedSignalProcessor
     for name in ("frame_size", "hop_size", "fps", "end"):
         assert getattr(back, name) == getattr(proc, name)
+
+
+def test_filter_functions_and_filterbank_classes_like_the_reference_tests(ref_filterbanks):
+    """tests/test_audio_filters.py:206-236 (log_frequencies), :376-448 (frequencies2bins, bins2frequencies),
+    :845-921 (MelFilterbank), :1023-1074 (LogarithmicFilterbank) on the drop-in module."""
+    from madmom_b200.audio import filters as F
+    from madmom_b200.audio.stft import fft_frequencies
+    for args in ((), (1,), (1, 2), (1, 2, 3, 4, 5)):
+        with pytest.raises(TypeError):
+            F.log_frequencies(*args)
+    result = F.log_frequencies(12, 20, 20000)
+    assert isinstance(result, np.ndarray) and result.dtype == float
+    assert len(F.log_frequencies(6, 30, 17000)) == 55
+    assert np.allclose(F.log_frequencies(1, 100, 1000), [110., 220., 440., 880.])
+    assert np.allclose(F.log_frequencies(1, 100, 1000, 441), [110.25, 220.5, 441., 882.])
+    for args in ((), (1,), (1, 2, 3, 4)):
+        with pytest.raises(TypeError):
+            F.frequencies2bins(*args)
+    result = F.frequencies2bins([0, 1, 2, 3, 4], [0, 1, 2, 3, 4])
+    assert isinstance(result, np.ndarray) and np.issubdtype(result.dtype, np.integer)
+    assert np.allclose(result, [0, 1, 2, 3, 4])
+    assert np.allclose(F.frequencies2bins([0, 1, 1.1, 1.2, 2, 3, 3.5], [0, 1, 2, 3, 4]), [0, 1, 1, 1, 2, 3, 4])
+    assert np.allclose(F.frequencies2bins([0, 1, 2, 3, 11], [0, 1, 2, 3, 4]), [0, 1, 2, 3, 4])
+    assert np.allclose(F.frequencies2bins([-1, 0, 1, 2, 3, 4], [0, 1, 2, 3, 4]), [0, 0, 1, 2, 3, 4])
+    assert np.allclose(F.frequencies2bins([0, 1, 2, 3, 4, 5], [0, 2, 4]), [0, 1, 1, 2, 2, 2])
+    assert np.allclose(F.frequencies2bins([0, 1, 2, 3, 4, 5], [0, 2, 4], unique_bins=True), [0, 1, 2])
+    assert np.allclose(F.frequencies2bins([-1, 0, 1, 2, 3, 4], [0, 1, 2, 3, 4], unique_bins=True), [0, 1, 2, 3, 4])
+    for args in ((), (1,), (1, 2, 3)):
+        with pytest.raises(TypeError):
+            F.bins2frequencies(*args)
+    result = F.bins2frequencies([0, 1, 2, 3, 4], [0, 1, 2, 3, 4])
+    assert isinstance(result, np.ndarray) and result.dtype == float and np.allclose(result, [0, 1, 2, 3, 4])
+    assert np.allclose(F.bins2frequencies([0, 1, 2, 3, 4], [0, 1, 1.1, 1.2, 2, 3, 4]), [0, 1, 1.1, 1.2, 2])
+    assert np.allclose(F.bins2frequencies([-1, 0, 1, 2, 3, 4], [0, 1, 2, 3, 4]), [4, 0, 1, 2, 3, 4])
+    # LogarithmicFilterbank
+    filt = F.LogarithmicFilterbank(np.arange(20000))
+    assert isinstance(filt, F.LogarithmicFilterbank) and filt.dtype == F.FILTER_DTYPE
+    assert filt.bin_frequencies.dtype == float
+    with pytest.raises(NotImplementedError):
+        F.LogarithmicFilterbank(np.arange(20000), bands_per_octave=False)
+    assert isinstance(F.LogarithmicFilterbank.NUM_BANDS_PER_OCTAVE, int)
+    assert F.LogarithmicFilterbank.NUM_BANDS_PER_OCTAVE == 12
+    filt = F.LogarithmicFilterbank(np.arange(0, 20000, 20), num_bands=12)
+    assert np.allclose(filt.min(), 0) and np.allclose(filt.max(), 1) and filt.shape == (1000, 81)
+    filt = F.LogarithmicFilterbank(np.arange(0, 20000, 20), num_bands=12, unique_filters=False)
+    assert np.allclose(filt.min(), 0) and np.allclose(filt.max(), 1) and filt.shape == (1000, 108)
+    filt = F.LogarithmicFilterbank(fft_frequencies(1024, 44100))
+    assert filt.num_bands == 81 and filt.num_bands_per_octave == 12 and filt.num_bins == 1024
+    assert np.allclose(filt.min(), 0) and np.allclose(filt.fmin, 43.066406) and np.allclose(filt.fmax, 16731.298828)
+    assert np.allclose(filt.center_frequencies, ref_filterbanks["N2048_b12_norm_center"])
+    corner = np.asarray(filt.corner_frequencies)
+    assert corner.shape == (81, 2) and np.all(corner[:, 0] <= filt.center_frequencies)
+    assert np.all(corner[:, 1] >= filt.center_frequencies)
+    # MelFilterbank
+    filt = F.MelFilterbank(np.arange(20000))
+    assert isinstance(filt, F.MelFilterbank) and filt.dtype == F.FILTER_DTYPE and filt.bin_frequencies.dtype == float
+    assert isinstance(F.MelFilterbank.FMIN, float) and isinstance(F.MelFilterbank.FMAX, float)
+    assert isinstance(F.MelFilterbank.NUM_BANDS, int) and isinstance(F.MelFilterbank.NORM_FILTERS, bool)
+    assert isinstance(F.MelFilterbank.UNIQUE_FILTERS, bool)
+    assert (F.MelFilterbank.FMIN, F.MelFilterbank.FMAX, F.MelFilterbank.NUM_BANDS) == (20., 17000., 40)
+    assert F.MelFilterbank.NORM_FILTERS is True and F.MelFilterbank.UNIQUE_FILTERS is True
+    filt = F.MelFilterbank(np.arange(1000) * 20, 10)
+    assert filt.num_bands == 10 and filt.num_bins == 1000 and filt.fmin == 40 and filt.fmax == 16980
+    assert np.allclose(filt.min(), 0) and np.allclose(filt.max(), 0.0714286)
+    assert np.allclose(filt.center_frequencies, [260, 580, 1020, 1600, 2380, 3420, 4820, 6700, 9180, 12520])
+    assert np.allclose(filt.corner_frequencies, [[40, 560], [280, 1000], [600, 1580], [1040, 2360], [1620, 3400],
+                                                 [2400, 4800], [3440, 6680], [4840, 9160], [6720, 12500],
+                                                 [9200, 16980]])
+    filt = F.MelFilterbank(np.fft.fftfreq(2048, 1. / 44100)[:1024])
+    assert np.allclose(filt.min(), 0) and np.allclose(filt.max(), 1. / 3)
+    assert np.allclose(filt.center_frequencies[:4], [86.132812, 150.732422, 215.332031, 279.931640])
+    assert np.allclose(filt.corner_frequencies[-1], [14470.312500, 16968.164062])

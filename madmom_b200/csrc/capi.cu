@@ -319,6 +319,24 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
     const double a = -2.0 * PI * (double)k / (double)N;
     tw64[k] = make_double2(std::cos(a), std::sin(a));
   }
+  // compact copies for stft64.cu, behind the natural table (same doubles, so the same results): per radix-4 pass
+  // with first-stage half-size H the H first-stage twiddles W_2H^m and the H / 2 second-stage twiddles W_H^m, each
+  // contiguous (a warp's 32 loads are one 512-byte run instead of 32 lines), then the split's twiddles in the
+  // bit-reversed order the split walks them, W_N^brev(2 p')
+  {
+    const int M = N / 2;
+    int log_m = 0;
+    while ((1 << log_m) < M) ++log_m;
+    for (int H = M / 2; H >= 2; H /= 4) {
+      for (int m = 0; m < H; ++m) tw64.push_back(tw64[(size_t)m * (N / (2 * H))]);
+      for (int m = 0; m < H / 2; ++m) tw64.push_back(tw64[(size_t)m * (N / H)]);
+    }
+    for (int pp = 0; pp < M / 2; ++pp) {
+      unsigned v = (unsigned)(2 * pp), r = 0;
+      for (int b = 0; b < log_m; ++b) { r = (r << 1) | (v & 1u); v >>= 1; }
+      tw64.push_back(tw64[r]);
+    }
+  }
   FbSchedule sch;
   build_schedule(cfg, K, woff, sch);
   p->n_passes = (int)sch.pass.size(); p->max_q = sch.max_q; p->b_pad = sch.b_pad; p->w_floats = (int)sch.w.size();

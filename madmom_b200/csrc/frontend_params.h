@@ -178,7 +178,7 @@ struct Stft64Params {
   int32_t origin, circular_shift, include_nyquist, spec_log_mode;
   float mul, add;
   const double* win;             // N doubles: fft_window as the reference multiplies it (float64, unscaled)
-  const double2* tw;             // N / 2 doubles2: W_N^k
+  const double2* tw;             // N / 2 doubles2: W_N^k, then the compact per-pass and split copies (capi.cu)
   float2* out_stft; int64_t ld_stft;
   float* out_spec;  int64_t ld_spec;
 };

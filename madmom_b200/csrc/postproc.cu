@@ -549,14 +549,39 @@ __global__ void __launch_bounds__(256, 2) complex_flux_cover_kernel(
 // One warp per frame: a reduction over the bins of a magnitude spectrogram and / or a complex STFT with lags
 // of one or two frames (madmom/features/onsets.py:102-160, 320-581).  Frames before the start of the row's signal
 // count as in the reference (zero rows of the lagged matrices).
-__device__ __forceinline__ float wrap_to_pi(float x) {
-  // np.mod(x + pi, 2 pi) - pi in float32 (result of mod has the sign of the divisor)
-  const float pi = 3.14159265358979323846f, two_pi = 6.28318530717958647692f;
-  float r = fmodf(x + pi, two_pi);
-  if (r < 0.0f) r += two_pi;
-  return r - pi;
-}
 __device__ __forceinline__ float cabs2(float2 z) { return sqrtf(z.x * z.x + z.y * z.y); }
+
+// np.angle / atan2(y, x) for the phase-based functions: octant reduction to t = min / max in [0, 1], atan(t) = t P(t^2)
+// with the 7-term minimax polynomial of the front end's local-group-delay stage (frame_fft.cuh; 3.2e-7 rad), then the
+// reflections.  Exact on the axes (0, +-pi/2, +-pi with the signs of atan2, signed zeros included), which is what the
+// pinned bin-0 phases need.  libm's atan2f made the phase kernels compute-bound at 0.17 - 0.4 of the HBM bandwidth.
+__device__ __forceinline__ float fast_atan2f(float y, float x) {
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+  const float t = mx > 0.0f ? __fdividef(mn, mx) : 0.0f;
+  const float u = t * t;
+  float p = 0.00681148456f;
+  p = fmaf(p, u, -0.0336031997f);
+  p = fmaf(p, u, 0.0796223719f);
+  p = fmaf(p, u, -0.132332626f);
+  p = fmaf(p, u, 0.198077921f);
+  p = fmaf(p, u, -0.333173652f);
+  p = fmaf(p, u, 0.999996111f);
+  float r = p * t;
+  if (ay > ax) r = 1.57079632679489661923f - r;
+  if (__float_as_int(x) < 0) r = 3.14159265358979323846f - r;       // sign bit: -0.0 counts like atan2's
+  return copysignf(r, y);
+}
+
+// z times the power of two that brings max(|re|, |im|) into [1, 2): exact, keeps the argument, and lets a product of
+// four such factors neither overflow nor underflow (phase_deviation counts a bin at -200 dB like a loud one).  Zero
+// counts as 1, i.e. phase 0 like np.angle(0).
+__device__ __forceinline__ float2 unit_scaled(float2 z) {
+  const float mx = fmaxf(fabsf(z.x), fabsf(z.y));
+  if (!(mx > 0.0f)) return make_float2(1.0f, 0.0f);
+  const float sc = __int_as_float(0x7f000000 - (__float_as_int(mx) & 0x7f800000));       // 2^-exponent(mx)
+  return make_float2(z.x * sc, z.y * sc);
+}
 
 // X[t-1] |.| exp(i (2 phi[t-1] - phi[t-2])) without trigonometry: s1 u1^2 conj(u2), u = X / |X| (1 when X = 0)
 __device__ __forceinline__ float2 cd_target(float2 x1, float2 x2, bool have2) {
@@ -608,9 +633,13 @@ __global__ void __launch_bounds__(256) spectral_odf_kernel(int32_t mode, const f
         const float m = cabs2(x0);
         acc2 += m;
         if (t >= 2) {
-          const float2 x1 = stft[(row - 1) * ld_stft + k], x2 = stft[(row - 2) * ld_stft + k];
-          const float p0 = atan2f(x0.y, x0.x), p1 = atan2f(x1.y, x1.x), p2 = atan2f(x2.y, x2.x);
-          const float pd = wrap_to_pi(p0 - 2.0f * p1 + p2);
+          // wrap(phi0 - 2 phi1 + phi2) is the argument of x0 conj(x1)^2 x2: one arctangent instead of three and no
+          // wrap (only the magnitude of the result is used, so +pi and -pi are the same)
+          const float2 u0 = unit_scaled(x0), u1 = unit_scaled(stft[(row - 1) * ld_stft + k]);
+          const float2 u2 = unit_scaled(stft[(row - 2) * ld_stft + k]);
+          const float2 a = make_float2(u0.x * u1.x + u0.y * u1.y, u0.y * u1.x - u0.x * u1.y);    // u0 conj(u1)
+          const float2 b = make_float2(u2.x * u1.x + u2.y * u1.y, u2.y * u1.x - u2.x * u1.y);    // u2 conj(u1)
+          const float pd = fast_atan2f(a.x * b.y + a.y * b.x, a.x * b.x - a.y * b.y);
           acc += fabsf(mode == MMB_ODF_PHASE_DEV ? pd : pd * m);
         }
       }
@@ -723,30 +752,44 @@ extern "C" MMB_API int mmb_peak_picking(const float* act_dev, const int64_t* seg
 // dd = p[k+1] - p[k] and numpy's unwrap rule  ddmod = mod(dd + pi, 2 pi) - pi,  ddmod = pi where it came out as -pi for
 // dd > 0,  correction = ddmod - dd where |dd| >= pi, else 0.
 namespace {
+// One warp per row, lanes over the bins: the phase of bin k + 1 comes from the next lane by shuffle (lane 31 takes
+// the arctangent of its right neighbour itself), loads and stores are coalesced and nothing divides.
 __global__ void __launch_bounds__(256) phase_lgd_kernel(const float2* __restrict__ stft, int64_t ld_stft,
                                                         float* __restrict__ phase, int64_t ld_phase,
                                                         float* __restrict__ lgd, int64_t ld_lgd, int64_t rows,
                                                         int32_t cols) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= rows * cols) return;
-  const int64_t row = i / cols;
-  const int k = (int)(i - row * cols);
-  const float2 z = stft[row * ld_stft + k];
-  const float p0 = atan2f(z.y, z.x);
-  if (phase) phase[row * ld_phase + k] = p0;
-  if (lgd) {
-    float v = 0.0f;
-    if (k + 1 < cols) {
-      const float pi = 3.14159265358979323846f, two_pi = 6.28318530717958647692f;
-      const float2 z1 = stft[row * ld_stft + k + 1];
-      const float dd = atan2f(z1.y, z1.x) - p0;
-      float ddmod = fmodf(dd + pi, two_pi);
-      if (ddmod < 0.0f) ddmod += two_pi;                 // np.mod: result has the sign of the divisor
-      ddmod -= pi;
-      if (ddmod == -pi && dd > 0.0f) ddmod = pi;
-      v = fabsf(dd) < pi ? -dd : -ddmod;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float2* src = stft + row * ld_stft;
+  const float pi = 3.14159265358979323846f, two_pi = 6.28318530717958647692f;
+  for (int k0 = 0; k0 < cols; k0 += 32) {                    // warp-uniform trip count: the shuffle needs all lanes
+    const int k = k0 + lane;
+    float p0 = 0.0f;
+    if (k < cols) {
+      const float2 z = src[k];
+      p0 = fast_atan2f(z.y, z.x);
+      if (phase) phase[row * ld_phase + k] = p0;
     }
-    lgd[row * ld_lgd + k] = v;
+    if (lgd) {
+      float pn = __shfl_down_sync(0xffffffffu, p0, 1);
+      if (lane == 31 && k + 1 < cols) {
+        const float2 z1 = src[k + 1];
+        pn = fast_atan2f(z1.y, z1.x);
+      }
+      if (k < cols) {
+        float v = 0.0f;
+        if (k + 1 < cols) {
+          const float dd = pn - p0;
+          float ddmod = fmodf(dd + pi, two_pi);
+          if (ddmod < 0.0f) ddmod += two_pi;                 // np.mod: result has the sign of the divisor
+          ddmod -= pi;
+          if (ddmod == -pi && dd > 0.0f) ddmod = pi;
+          v = fabsf(dd) < pi ? -dd : -ddmod;
+        }
+        lgd[row * ld_lgd + k] = v;
+      }
+    }
   }
 }
 }  // namespace
@@ -757,8 +800,7 @@ extern "C" MMB_API int mmb_phase_lgd(const void* stft_dev, int64_t ld_stft, floa
       (phase_dev && ld_phase < cols) || (lgd_dev && ld_lgd < cols))
     return mmb::set_error(MMB_E_INVALID, "mmb_phase_lgd: invalid argument");
   if (rows == 0) return MMB_OK;
-  const int64_t n = rows * cols;
-  phase_lgd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  phase_lgd_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
       (const float2*)stft_dev, ld_stft, phase_dev, ld_phase, lgd_dev, ld_lgd, rows, cols);
   return cudaGetLastError() == cudaSuccess ? MMB_OK : mmb::set_error(MMB_E_CUDA, "mmb_phase_lgd: kernel launch failed");
 }

@@ -628,3 +628,44 @@ def test_complex_flux_kernel_ragged_signals(n_bins, B, monkeypatch):
     args3 = (big_l, big_d, args[2], args[3])
     a = _lib.complex_flux(*args3, rows_per_signal=37).cpu().numpy()
     assert np.array_equal(a, other("MMB_CF_GENERIC", args=args3, rows_per_signal=37))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cols", [1024, 512, 1025])
+def test_phase_deviation_kernels_against_numpy(cols):
+    """The three phase-deviation functions on random complex matrices with signals of 1, 2, 3 and many rows back to
+    back against numpy's definition (madmom/features/onsets.py:320-437: mean |wrap(phi[t] - 2 phi[t-1] + phi[t-2])|,
+    weighted by |X|, normalised), within 1e-5 + 1e-4 |ref| for every row.  The kernel takes the wrapped second
+    difference as the argument of x0 conj(x1)^2 x2 (one arctangent per bin): bins of very different magnitude, a
+    silent frame (phase 0 like np.angle(0)) and bins on the negative real axis are in the input."""
+    from madmom_b200 import _lib
+    rng = np.random.default_rng(cols)
+    lens = [1, 2, 3, 1, 400, 2, 1700, 333, 1]
+    rows = sum(lens)
+    x = (rng.standard_normal((rows, cols)) + 1j * rng.standard_normal((rows, cols))).astype(np.complex64)
+    x *= (10.0 ** rng.uniform(-12, 3, size=(rows, cols))).astype(np.float32)      # 300 dB of dynamic range
+    x[5, :] = 0
+    x[40, 3] = -1.0
+    x[41:44, 7] = [-2.0, -3.0, -0.5]
+    seg = np.concatenate(([0], np.cumsum(lens))).astype(np.int64)
+    dev = torch.device("cuda:0")
+    xs, segs = torch.from_numpy(x).to(dev), torch.from_numpy(seg).to(dev)
+    for mode in ("phase_deviation", "weighted_phase_deviation", "normalized_weighted_phase_deviation"):
+        got = _lib.spectral_odf(mode, stft=xs, seg_offsets=segs).cpu().numpy()
+        want = np.zeros(rows)
+        for s in range(len(lens)):
+            a, e = seg[s], seg[s + 1]
+            ph = np.angle(x[a:e].astype(np.complex128))
+            pd = np.zeros_like(ph)
+            if e - a > 2:
+                pd[2:] = ph[2:] - 2 * ph[1:-1] + ph[:-2]
+            pd = np.mod(pd + np.pi, 2 * np.pi) - np.pi
+            mag = np.abs(x[a:e]).astype(np.float64)
+            if mode == "phase_deviation":
+                want[a:e] = np.mean(np.abs(pd), axis=1)
+            elif mode == "weighted_phase_deviation":
+                want[a:e] = np.mean(np.abs(pd * mag), axis=1)
+            else:
+                want[a:e] = np.mean(np.abs(pd * mag), axis=1) / (np.mean(mag, axis=1) + np.finfo(float).eps)
+        err = np.abs(got - want) - (1e-5 + 1e-4 * np.abs(want))
+        assert err.max() <= 0, (mode, int(err.argmax()), got[err.argmax()], want[err.argmax()])

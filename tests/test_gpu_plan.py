@@ -287,3 +287,64 @@ def test_errors():
         plan.run(pcm, units, {"log": torch.zeros((23, 0), device="cuda")})
     with pytest.raises(ValueError):
         plan.run(pcm, units, {})
+
+
+@pytest.mark.parametrize("seed", range(int(__import__("os").environ.get("MMB_FUZZ_SEEDS", "40"))))
+def test_random_recipes_vs_oracle(seed):
+    """Differential test over the parameter space the plan accepts: frame size, hop (integer and fractional), bands
+    per octave, filter normalisation, log scaling, lag ratio, frequency max-filter, signed / rectified differences,
+    circular shift, origin, chunk size, int16 / float32 samples, on a ragged batch of random track lengths (shorter
+    than a frame, shorter than a hop, one sample).  Every stage of every track against the oracle.
+    Bounds: raw bins one float32 rounding; features 1e-5 + 1e-4 |ref| for mul / add <= 10 (the reference's recipes use
+    1 and 5: the logarithm multiplies the FP32 transform's absolute noise floor by mul / (y ln 10)).  N = 1024 packs
+    two frames into one complex FFT, so a frame's bins carry rounding noise of its partner's: the absolute term grows
+    by 3e-7 x the track's largest magnitude x the widest band's weight sum (a frame that is exactly silent after
+    windowing reads 1e-5 instead of 0 next to a full-scale one; the reference transforms every frame on its own).
+    40 seeds in the suite; MMB_FUZZ_SEEDS=400 was run in round 2 and is how both limits were found."""
+    from oracle import frontend as O
+    from madmom_b200.synth import make_track
+    rng = np.random.default_rng(7000 + seed)
+    N = int(rng.choice([1024, 2048, 4096]))
+    hop = float(rng.choice([441., 220.5, 882., 512., 147., 300.25, 1000.]))
+    bpo = int(rng.choice([3, 6, 12, 24]))
+    norm = bool(rng.integers(2))
+    mul = float(rng.choice([1., 5., 0.5, 10.]))
+    add = float(rng.choice([1., 1., 2.5]))
+    ratio = float(rng.choice([0.25, 0.5, 0.75]))
+    max_bins = [None, 3, 3, 5][int(rng.integers(4))]
+    positive = bool(rng.integers(4) != 0)
+    circ = bool(rng.integers(4) == 0)
+    origin = int(rng.choice([0, 0, 0, N // 2 - 1, -N // 2, 37, -250]))
+    chunk_frames = int(rng.choice([0, 0, 7, 13, 64]))
+    dtype = np.float32 if rng.integers(3) == 0 else np.int16
+    lens = [int(v) for v in rng.integers(1, 40000, size=5)] + [1, int(hop) - 1 or 1, N - 1, N, N + 1]
+    rng.shuffle(lens)
+    tracks = []
+    for i, n in enumerate(lens):
+        x = make_track(9000 + 100 * seed + i, num_samples=n)
+        tracks.append((x / 32767.).astype(np.float32) if dtype == np.float32 else x)
+    plan, recipe = _plan_for(dtype, N, hop, bpo, norm, mul=mul, add=add, ratio=ratio, max_bins=max_bins,
+                             positive=positive, circ=circ, origin=origin, chunk_frames=chunk_frames)
+    got, T = _run_all(plan, tracks, hop)
+    what = "seed %d: N=%d hop=%g bpo=%d norm=%s mul=%g add=%g ratio=%g max_bins=%s pos=%s circ=%s origin=%d chunk=%d %s" % (
+        seed, N, hop, bpo, norm, mul, add, ratio, max_bins, positive, circ, origin, chunk_frames, np.dtype(dtype).name)
+    fb = O.logarithmic_filterbank(O.fft_frequencies(N // 2, 44100), bpo, 30., 17000., 440., norm, True)
+    widest = float(np.asarray(fb).sum(axis=0).max())
+    r0 = 0
+    for x, t in zip(tracks, T):
+        assert t == O.num_frames(len(x), hop), what
+        ref = O.run_recipe(x, recipe, stages=True)
+        sl = {k: v[r0:r0 + t] for k, v in got.items()}
+        w = what + " | track of %d samples" % len(x)
+        assert_bins_close(sl["stft"], ref["stft"], w + " stft")
+        assert_bins_close(sl["spec"], ref["spec"], w + " spec")
+        # packed pairs (N = 1024 only): the partner frame's rounding noise on top of the standard 1e-5, see the
+        # docstring; through log10(mul x + add) it is multiplied by mul / (add ln 10), a difference takes two of them,
+        # the flux at most one per band.  For N = 2048 and 4096 `extra` is 0 and the standard bound applies.
+        extra = 3e-7 * float(np.abs(ref["spec"]).max()) * widest if N == 1024 and t else 0.0
+        extra_log = extra * mul / (add * np.log(10.))
+        assert_close(sl["filt"], ref["filt"], atol=1e-5 + extra, what=w + " filt")
+        assert_close(sl["log"], ref["log"], atol=1e-5 + extra_log, what=w + " log")
+        assert_close(sl["diff"], ref["diff"], atol=1e-5 + 2 * extra_log, what=w + " diff")
+        assert_close(sl["odf"], ref["odf"], atol=1e-5 + 2 * extra_log * ref["diff"].shape[1], what=w + " odf")
+        r0 += t

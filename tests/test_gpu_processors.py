@@ -669,3 +669,45 @@ def test_phase_deviation_kernels_against_numpy(cols):
                 want[a:e] = np.mean(np.abs(pd * mag), axis=1) / (np.mean(mag, axis=1) + np.finfo(float).eps)
         err = np.abs(got - want) - (1e-5 + 1e-4 * np.abs(want))
         assert err.max() <= 0, (mode, int(err.argmax()), got[err.argmax()], want[err.argmax()])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(int(__import__("os").environ.get("MMB_FUZZ_SEEDS", "24"))))
+def test_random_long_signal_shards_are_bit_identical(seed):
+    """The property the multi-GPU path rests on, over random cases: a signal of random length cut into the frame
+    ranges of 2 .. 9 ranks (more ranks than frames included), any frame size, integer and fractional hops, lags of
+    1 .. 3 frames, with and without the frequency max-filter -- each rank's rows computed from its own PCM slice with
+    its halo (parallel.LongSignalFrontEnd.run_local), concatenated like the all-gather does -- equals the unsharded
+    launch bit for bit, float32 PCM included."""
+    from madmom_b200 import parallel, recipe as R
+    from madmom_b200.batch import BatchFrontEnd
+    from madmom_b200.synth import make_track
+    rng = np.random.default_rng(8000 + seed)
+    N = int(rng.choice([1024, 2048, 4096]))
+    hop = float(rng.choice([441., 220.5, 882., 300.25, 147., 1000.]))
+    rec = R.SUPERFLUX.replace(frame_size=N, hop_size=hop, num_bands=int(rng.choice([6, 12, 24])),
+                              diff_ratio=float(rng.choice([0.25, 0.5, 0.75])),
+                              diff_max_bins=[None, 3][int(rng.integers(2))])
+    n = int(rng.choice([1, 17, int(hop), N - 1, N + 1, int(rng.integers(2000, 300000)), int(rng.integers(2000, 300000))]))
+    dtype = np.float32 if rng.integers(4) == 0 else np.int16
+    x = make_track(12000 + seed, num_samples=n)
+    if dtype == np.float32:
+        x = (x / 32767.).astype(np.float32)
+    whole = BatchFrontEnd(rec, dtype).run_device(torch.from_numpy(x).cuda(), [len(x)], ("diff", "odf"))
+    T = whole["diff"].shape[0]
+    fe = parallel.LongSignalFrontEnd(rec, dtype)
+    for world in sorted(set(int(w) for w in rng.integers(2, 10, size=3))):
+        parts = {"diff": [], "odf": []}
+        covered = 0
+        for rank in range(world):
+            sh = fe.shard(len(x), world, rank)
+            assert sh.frame_first == min(covered, T) or sh.frame_count == 0
+            covered += sh.frame_count
+            local = fe.run_local(torch.from_numpy(x[sh.sample_lo:sh.sample_hi].copy()).cuda(), sh, ("diff", "odf"))
+            for k in parts:
+                parts[k].append(local[k])
+        assert covered == T
+        for k in parts:
+            full = torch.cat(parts[k])[:T]
+            assert torch.equal(full, whole[k]), "seed %d N=%d hop=%g n=%d world=%d %s %s" % (
+                seed, N, hop, n, world, np.dtype(dtype).name, k)

@@ -276,6 +276,37 @@ def test_host_path_splits_a_long_unit(N, ratio, monkeypatch):
         assert np.array_equal(out[k], dev[k]), (N, k)
 
 
+@pytest.mark.parametrize("seed", range(int(__import__("os").environ.get("MMB_FUZZ_SEEDS", "16"))))
+def test_random_host_path_equals_device_path(seed, monkeypatch):
+    """mmb_run_host (pinned staging, groups of units on three streams, over-long units cut into frame ranges) against
+    the device path on random batches: ragged track lengths from one sample to a few megabytes, random group size,
+    frame size, hop, lag, int16 / float32 -- every output bit-identical."""
+    from madmom_b200 import _lib
+    from madmom_b200.synth import make_track
+    rng = np.random.default_rng(9000 + seed)
+    N = int(rng.choice([1024, 2048, 4096]))
+    hop = float(rng.choice([441., 220.5, 882., 300.25]))
+    dtype = np.float32 if rng.integers(3) == 0 else np.int16
+    lens = [int(v) for v in rng.integers(1, 60000, size=int(rng.integers(1, 7)))]
+    if rng.integers(2):
+        lens.insert(int(rng.integers(len(lens) + 1)), int(rng.integers(700000, 2500000)))       # one long unit
+    tracks = []
+    for i, n in enumerate(lens):
+        x = make_track(13000 + 50 * seed + i, num_samples=n)
+        tracks.append((x / 32767.).astype(np.float32) if dtype == np.float32 else x)
+    plan, _ = _plan_for(dtype, N, hop, int(rng.choice([6, 12, 24])), bool(rng.integers(2)),
+                        ratio=float(rng.choice([0.25, 0.5, 0.75])), max_bins=[None, 3][int(rng.integers(2))])
+    dev, T = _run_all(plan, tracks, hop)
+    units = _lib.make_units(lens, T)
+    rows = sum(T)
+    monkeypatch.setenv("MMB_HOST_GROUP_MB", str(int(rng.choice([1, 2, 8, 64]))))
+    names = [k for k in ("log", "diff", "odf", "spec", "filt") if rng.integers(3) or k == "diff"]
+    out = {k: np.full(dev[k].shape, np.nan, np.float32) for k in names}
+    plan.run_host(np.concatenate(tracks), units, out)
+    for k in names:
+        assert np.array_equal(out[k], dev[k]), (seed, N, hop, lens, k)
+
+
 def test_errors():
     from madmom_b200 import _lib
     with pytest.raises(NotImplementedError):

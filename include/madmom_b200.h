@@ -208,7 +208,8 @@ MMB_API int mmb_complex_flux(const float* lgd_dev, int64_t ld_lgd, const float* 
 
 /* phase() and local_group_delay() of madmom/audio/stft.py:136-179 (the Phase / LocalGroupDelay classes, :556-708) on a
  * complex64 STFT on the device (rows x cols, re / im pairs): phase = angle(stft); lgd[:, k] = unwrap(phase)[k] -
- * unwrap(phase)[k + 1] with numpy's unwrap rule, last column 0.  Either output may be null. */
+ * unwrap(phase)[k + 1] with numpy's unwrap rule, last column 0.  Either output may be null.  The arctangent is a
+ * polynomial one (3.2e-7 rad; exact on the axes with atan2's signs, signed zeros included). */
 MMB_API int mmb_phase_lgd(const void* stft_dev, int64_t ld_stft, float* phase_dev, int64_t ld_phase, float* lgd_dev,
                           int64_t ld_lgd, int64_t rows, int32_t cols, void* stream);
 
@@ -236,7 +237,9 @@ MMB_API int mmb_run_host_interleaved(const mmb_plan* plan, const mmb_track* unit
  *   RECTIFIED_COMPLEX_DOMAIN rectified_complex_domain :552-581   the same over bins whose magnitude rose against t-d
  * The first three read a magnitude matrix `spec_dev` (any spectrogram: raw, filtered, logarithmic), the others the
  * complex64 STFT `stft_dev` (re, im pairs).  Rows before the start of a signal count as zero rows of the lagged
- * terms, as in the reference.  Signals: see mmb_complex_flux. */
+ * terms, as in the reference.  Signals: see mmb_complex_flux.  The three phase-deviation functions take the wrapped
+ * second difference as the argument of X[t] conj(X[t-1])^2 X[t-2] (one arctangent per bin, factors scaled by exact
+ * powers of two); a bin that is exactly zero counts as phase 0, like np.angle(0). */
 enum {
   MMB_ODF_HFC = 1, MMB_ODF_SPECTRAL_DIFF = 2, MMB_ODF_MKL = 3, MMB_ODF_PHASE_DEV = 4,
   MMB_ODF_WEIGHTED_PHASE_DEV = 5, MMB_ODF_NORM_WEIGHTED_PHASE_DEV = 6, MMB_ODF_COMPLEX_DOMAIN = 7,

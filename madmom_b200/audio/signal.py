@@ -81,6 +81,47 @@ def normalize(signal):
     return np.asanyarray(signal / scaling, dtype=signal.dtype)
 
 
+def energy(signal):
+    """Sum of the squared samples in float64, all channels together (madmom/audio/signal.py:332-365); one value per
+    frame for a FramedSignal."""
+    if isinstance(signal, FramedSignal):
+        return np.array([energy(frame) for frame in signal])
+    x = np.asarray(signal)
+    if np.iscomplexobj(x):
+        x = np.abs(x)
+    x = x.astype(float).ravel()
+    return float(np.dot(x, x))
+
+
+def root_mean_square(signal):
+    """sqrt(energy / number of samples) (madmom/audio/signal.py:368-392)."""
+    if isinstance(signal, FramedSignal):
+        return np.array([root_mean_square(frame) for frame in signal])
+    return float(np.sqrt(energy(signal) / np.asarray(signal).size))
+
+
+def sound_pressure_level(signal, p_ref=None):
+    """20 log10(rms / p_ref) in dB; p_ref defaults to the largest value of an integer sample type, 1 for floats;
+    silence gives the most negative finite float (madmom/audio/signal.py:395-438)."""
+    if isinstance(signal, FramedSignal):
+        return np.array([sound_pressure_level(frame) for frame in signal])
+    rms = root_mean_square(signal)
+    if p_ref is None:
+        dtype = np.asarray(signal).dtype
+        p_ref = float(np.iinfo(dtype).max) if np.issubdtype(dtype, np.integer) else 1.0
+    with np.errstate(divide="ignore"):
+        return float(np.nan_to_num(20.0 * np.log10(rms / p_ref)))
+
+
+def write_wave_file(signal, filename, sample_rate=None):
+    """Write the samples as a RIFF/WAVE file with scipy (madmom/io/audio.py:670-702)."""
+    from scipy.io import wavfile
+    if sample_rate is None:
+        sample_rate = int(signal.sample_rate)
+    wavfile.write(filename, rate=sample_rate, data=np.asarray(signal))
+    return filename
+
+
 def remix(signal, num_channels, channel=None):
     """Down-mix to mono (mean over channels cast back to the input dtype) or up-mix mono by repetition
     (madmom/audio/signal.py:170-223)."""
@@ -151,6 +192,22 @@ class Signal(np.ndarray):
         if self.sample_rate is None:
             return None
         return float(self.num_samples) / self.sample_rate
+
+    def write(self, filename):
+        return write_wave_file(self, filename)
+
+    def energy(self):
+        return energy(self)
+
+    def root_mean_square(self):
+        return root_mean_square(self)
+
+    rms = root_mean_square
+
+    def sound_pressure_level(self, p_ref=None):
+        return sound_pressure_level(self, p_ref)
+
+    spl = sound_pressure_level
 
 
 class SignalProcessor(Processor):

@@ -497,3 +497,95 @@ def test_filter_functions_and_filterbank_classes_like_the_reference_tests(ref_fi
     assert np.allclose(filt.min(), 0) and np.allclose(filt.max(), 1. / 3)
     assert np.allclose(filt.center_frequencies[:4], [86.132812, 150.732422, 215.332031, 279.931640])
     assert np.allclose(filt.corner_frequencies[-1], [14470.312500, 16968.164062])
+
+
+def test_remix_like_the_reference_tests(sample_pcm):
+    """TestMixFunction, tests/test_audio_signal.py:277-361, on the drop-in `remix`: shapes and dtypes of the mono and
+    multi-channel cases, channel selection, the integer mean, the unsupported conversion."""
+    from madmom_b200.audio.signal import Signal, remix
+    sig_1d = np.asarray([0, 0, 1, 0, 0, 1, 0, 0, 1], dtype=float)
+    sig_2d = np.asarray([[0, 0, 1, 0, 0, 1, 0, 0, 1], [1, 0, 1, 0, 1, 0, 1, 0, 1]], dtype=float).T
+    mono_2d = np.asarray([0.5, 0, 1, 0, 0.5, 0.5, 0.5, 0, 1], dtype=float)
+    for x, dt in ((sig_1d, float), (sig_1d.astype(int), int)):
+        r = remix(x, 1)
+        assert len(r) == len(x) and r.shape == x.shape and r.dtype == dt
+        for ch in (2, 3):
+            r = remix(x, ch)
+            assert len(r) == len(x) and r.shape == (len(x), ch) and r.dtype == dt
+    sig = Signal(sample_pcm, sample_rate=44100)
+    r = remix(sig, 1)
+    assert isinstance(r, Signal) and isinstance(r, np.ndarray) and r.dtype == np.int16
+    for x, dt in ((sig_2d, float), (sig_2d.astype(int), int)):
+        r = remix(x, 1)
+        assert len(r) == len(x) and r.shape == sig_1d.shape and r.dtype == dt
+        r = remix(x, 2)
+        assert len(r) == len(x) and r.shape == x.shape and r.dtype == dt
+    stereo = Signal(np.stack((sample_pcm, sample_pcm // 2), axis=1), sample_rate=44100)
+    for ch in (1, 2):
+        r = remix(stereo, ch)
+        assert isinstance(r, Signal) and isinstance(r, np.ndarray) and r.dtype == np.int16
+    with pytest.raises(NotImplementedError):
+        remix(sig_2d, 3)
+    r = remix(sig_2d, 1, channel=0)                                          # test_channel_selection
+    assert r.shape == sig_1d.shape and np.array_equal(r, sig_1d)
+    assert np.array_equal(remix(sig_2d, 1, channel=1), sig_2d[:, 1])
+    assert np.allclose(remix(sig_1d, 1), sig_1d)                             # test_values
+    assert np.allclose(remix(sig_2d.astype(int), 1), mono_2d.astype(int))
+    assert np.allclose(remix(sig_2d, 1), mono_2d)
+    assert np.allclose(remix(2 * sig_2d.astype(int), 1), 2 * mono_2d)
+
+
+def test_signal_class_like_the_reference_tests(sample_pcm, tmp_path):
+    """TestSignalClass, tests/test_audio_signal.py:696-795, on the drop-in Signal: types and values with and without a
+    sample rate, 2-D signals, num_channels, the sample file's samples, write / re-read, energy / rms / spl."""
+    from madmom_b200.audio.signal import Signal
+    sig_1d = np.asarray([0, 0, 1, 0, 0, 1, 0, 0, 1], dtype=float)
+    sig_2d = np.asarray([[0, 0, 1, 0, 0, 1, 0, 0, 1], [1, 0, 1, 0, 1, 0, 1, 0, 1]], dtype=float).T
+    r = Signal(sig_1d)
+    assert isinstance(r, Signal) and isinstance(r, np.ndarray) and r.dtype == float
+    assert r.start is None and r.stop is None and isinstance(r.num_samples, int) and r.sample_rate is None
+    assert isinstance(r.num_channels, int) and r.length is None and isinstance(r.ndim, int)
+    assert np.allclose(r, sig_1d) and len(r) == 9 and r.num_samples == 9 and r.num_channels == 1
+    r = Signal(sig_1d, 1)
+    assert r.dtype == float and isinstance(r.sample_rate, int) and isinstance(r.length, float)
+    assert np.allclose(r, sig_1d) and r.num_samples == 9 and r.sample_rate == 1 and r.length == 9
+    r = Signal(sig_2d, 12.3)
+    assert np.allclose(r, sig_2d) and len(r) == 9 and r.num_samples == 9 and r.sample_rate == 12.3
+    assert r.num_channels == 2 and r.length == 9 / 12.3 and r.ndim == 2
+    r = Signal(sig_2d, sample_rate=1, num_channels=1)
+    assert r.shape == (9,) and np.allclose(r, [0.5, 0, 1, 0, 0.5, 0.5, 0.5, 0, 1])
+    r = Signal(sample_pcm, sample_rate=44100)
+    assert np.allclose(r[:5], [-2494, -2510, -2484, -2678, -2833]) and len(r) == 123481
+    assert r.num_samples == 123481 and r.sample_rate == 44100 and r.num_channels == 1 and r.ndim == 1
+    assert np.allclose(r.length, 2.8)
+    path = str(tmp_path / "sample_copy.wav")                                 # test_write_method
+    r.write(path)
+    back = Signal(path)
+    assert back.dtype == np.int16 and back.sample_rate == 44100 and np.allclose(r, back)
+    s = Signal(sig_1d)                                                        # test_methods
+    assert np.allclose(s.energy(), 3) and np.allclose(s.rms(), 0.57735026919) and np.allclose(s.spl(), -4.7712125472)
+    s = Signal(sig_2d)
+    assert np.allclose(s.energy(), 8) and np.allclose(s.root_mean_square(), 2. / 3)
+    assert np.allclose(s.sound_pressure_level(), -3.52182518111)
+
+
+def test_energy_rms_spl_like_the_reference_tests():
+    """The frame-wise and silence cases of tests/test_audio_signal.py:600-693 (root_mean_square, sound_pressure_level)."""
+    from madmom_b200.audio.signal import FramedSignal, remix, root_mean_square, sound_pressure_level
+    sig_1d = np.asarray([0, 0, 1, 0, 0, 1, 0, 0, 1], dtype=float)
+    sig_2d = np.asarray([[0, 0, 1, 0, 0, 1, 0, 0, 1], [1, 0, 1, 0, 1, 0, 1, 0, 1]], dtype=float).T
+    assert isinstance(root_mean_square(sig_1d), float) and np.allclose(root_mean_square(np.zeros(100)), 0)
+    assert np.allclose(root_mean_square(FramedSignal(sig_1d, frame_size=4, hop_size=2)), [0, 0.5, 0.70710678, 0.5, 0.5])
+    assert np.allclose(root_mean_square(FramedSignal(sig_2d, frame_size=4, hop_size=2)),
+                       [0.35355339, 0.61237244, 0.70710678, 0.61237244, 0.61237244])
+    lowest = -np.finfo(float).max
+    assert np.allclose(sound_pressure_level(np.zeros(100)), lowest)
+    sinus = np.cos(np.linspace(0, 2 * np.pi * 100, 2 * 100 + 1))
+    assert np.allclose(sound_pressure_level(sinus), 0.)
+    sinus_int16 = (sinus * np.iinfo(np.int16).max).astype(np.int16)
+    assert np.allclose(sound_pressure_level(sinus_int16), 0., atol=1e-3)
+    assert np.allclose(sound_pressure_level(remix(sinus_int16, 2)), 0., atol=1e-3)
+    assert np.allclose(sound_pressure_level(FramedSignal(sig_1d, frame_size=4, hop_size=2)),
+                       [lowest, -6.0206, -3.0103, -6.0206, -6.0206])
+    assert np.allclose(sound_pressure_level(FramedSignal(sig_2d, frame_size=4, hop_size=2)),
+                       [-9.03089987, -4.25968732, -3.01029996, -4.25968732, -4.25968732])

@@ -48,6 +48,8 @@ def rescale(signal, dtype=np.float32):
         raise ValueError("only float dtypes are supported, not %s." % dtype)
     if np.issubdtype(signal.dtype, np.floating):
         return signal.astype(dtype)
+    if not np.issubdtype(signal.dtype, np.integer):
+        raise ValueError("only integer and float signals can be rescaled, not %s." % signal.dtype)
     return signal.astype(dtype) / np.iinfo(signal.dtype).max
 
 
@@ -79,6 +81,23 @@ def normalize(signal):
             raise ValueError("only float and np.int16/32 dtypes supported, not %s." % signal.dtype)
         scaling /= np.iinfo(signal.dtype).max
     return np.asanyarray(signal / scaling, dtype=signal.dtype)
+
+
+def trim(signal, where="fb"):
+    """Cut leading ('f') and / or trailing ('b') sample frames in which every channel is zero
+    (madmom/audio/signal.py:295-329)."""
+    where = where.upper()
+    x = np.asarray(signal)
+    nonzero = np.nonzero(x if x.ndim == 1 else np.abs(x).sum(axis=tuple(range(1, x.ndim))))[0]
+    first, last = 0, len(x)
+    if len(nonzero):
+        if "F" in where:
+            first = int(nonzero[0])
+        if "B" in where:
+            last = int(nonzero[-1]) + 1
+    elif "F" in where:
+        first = last                                         # all zeros: nothing is left, like np.trim_zeros
+    return signal[first:last]
 
 
 def energy(signal):

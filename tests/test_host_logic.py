@@ -589,3 +589,70 @@ def test_energy_rms_spl_like_the_reference_tests():
                        [lowest, -6.0206, -3.0103, -6.0206, -6.0206])
     assert np.allclose(sound_pressure_level(FramedSignal(sig_2d, frame_size=4, hop_size=2)),
                        [-9.03089987, -4.25968732, -3.01029996, -4.25968732, -4.25968732])
+
+
+def test_gain_normalize_rescale_trim_like_the_reference_tests(sample_pcm):
+    """TestAdjustGainFunction, TestAttenuateFunction, TestNormalizeFunction, TestRescaleFunction, TestTrimFunction
+    (tests/test_audio_signal.py:95-276, 447-555) on the drop-in functions: shapes, dtypes, values on the small
+    signals, the integer truncation, the errors."""
+    from madmom_b200.audio.signal import Signal, adjust_gain, attenuate, normalize, rescale, trim
+    sig_1d = np.asarray([0, 0, 1, 0, 0, 1, 0, 0, 1], dtype=float)
+    sig_2d = np.asarray([[0, 0, 1, 0, 0, 1, 0, 0, 1], [1, 0, 1, 0, 1, 0, 1, 0, 1]], dtype=float).T
+    sig = Signal(sample_pcm, sample_rate=44100)
+    for fn in (adjust_gain, attenuate):
+        for x in (sig_1d, sig_1d.astype(np.int16), sig_2d, sig_2d.astype(int)):
+            r = fn(x, 0)
+            assert type(r) == type(x) and r.shape == x.shape and r.dtype == x.dtype and np.allclose(r, x)
+        r = fn(sig, 0)
+        assert isinstance(r, Signal) and r.dtype == np.int16
+    assert np.allclose(adjust_gain(sig_1d, -10), 0.31622777 * sig_1d)
+    assert np.allclose(adjust_gain(sig_1d, 10), 3.1622777 * sig_1d)
+    assert np.allclose(adjust_gain(sig_1d.astype(int), -5), 0 * sig_1d)
+    assert np.allclose(adjust_gain(sig_2d, -3), 0.70794578 * sig_2d)
+    assert np.allclose(adjust_gain(sig_2d.astype(np.int16), -1), 0 * sig_2d)
+    with pytest.raises(ValueError):
+        adjust_gain(sig_2d.astype(np.int16), +60)
+    assert np.allclose(attenuate(sig_1d, 10), 0.31622777 * sig_1d)
+    assert np.allclose(attenuate(sig_1d, -10), 3.1622777 * sig_1d)
+    assert np.allclose(attenuate(sig_1d.astype(int), 5), 0 * sig_1d)
+    assert np.allclose(attenuate(sig_2d, 3), 0.70794578 * sig_2d)
+    assert np.allclose(attenuate(sig_2d.astype(np.int16), 1), 0 * sig_2d)
+    with pytest.raises(ValueError):
+        attenuate(sig_2d.astype(np.int16), -10)
+    for x in (sig_1d, sig_1d.astype(np.int16), sig_2d, sig_2d.astype(np.int32)):       # normalize
+        r = normalize(x)
+        assert r.shape == x.shape and r.dtype == x.dtype
+    r = normalize(sig)
+    assert isinstance(r, Signal) and r.dtype == np.int16
+    assert np.allclose(normalize(sig_1d), sig_1d) and np.allclose(normalize(sig_1d * 0.5), sig_1d)
+    assert np.max(normalize(sig_1d * 0.5)) == 1
+    r = normalize(10 * sig_1d.astype(np.int16))
+    assert np.allclose(r, sig_1d * 32767) and np.max(r) == 32767
+    r = normalize(sig_2d * 4 - 2)
+    assert np.allclose(r, sig_2d * 2 - 1) and r.max() == 1 and r.min() == -1
+    r = normalize(3 * sig_2d.astype(np.int32))
+    assert np.allclose(r, sig_2d * 2147483647) and np.max(r) == 2147483647
+    with pytest.raises(ValueError):
+        normalize(sig_2d.astype(np.int64))
+    r = rescale(sig_1d, float)                                                          # rescale
+    assert r.shape == sig_1d.shape and r.dtype == float and np.allclose(r, sig_1d)
+    r = rescale(sig)
+    assert isinstance(r, Signal) and r.dtype == np.float32
+    assert np.allclose(r[:6], [-0.07611316, -0.07660146, -0.07580798, -0.08172857, -0.08645894, -0.08212531])
+    r = rescale(sig_2d, np.float16)
+    assert r.shape == sig_2d.shape and r.dtype == np.float16 and np.allclose(r, sig_2d)
+    assert rescale(sig, float).dtype == float
+    for bad in ((sig_2d, complex), (sig_2d, int)):
+        with pytest.raises(ValueError):
+            rescale(*bad)
+    with pytest.raises(ValueError):
+        rescale(np.ones(10, dtype=complex))
+    r = trim(sig_1d)                                                                    # trim
+    assert type(r) == type(sig_1d) and r.dtype == sig_1d.dtype and np.allclose(r, [1, 0, 0, 1, 0, 0, 1])
+    r = trim(sig)
+    assert isinstance(r, Signal) and r.ndim == 1 and r.dtype == np.int16
+    assert trim(sig_2d).shape == sig_2d.shape                   # leading zeros in one channel only stay
+    both = np.tile(np.arange(5), 2).reshape(2, 5).T
+    r = trim(both)
+    assert r.shape == (4, 2) and np.allclose(r[:, 0], np.arange(1, 5)) and np.allclose(r[:, 1], np.arange(1, 5))
+    assert np.allclose(trim(np.arange(5, 0, -1)), [5, 4, 3, 2, 1])

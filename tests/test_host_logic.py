@@ -656,3 +656,35 @@ def test_gain_normalize_rescale_trim_like_the_reference_tests(sample_pcm):
     r = trim(both)
     assert r.shape == (4, 2) and np.allclose(r[:, 0], np.arange(1, 5)) and np.allclose(r[:, 1], np.arange(1, 5))
     assert np.allclose(trim(np.arange(5, 0, -1)), [5, 4, 3, 2, 1])
+
+
+def test_filterbank_base_class_like_the_reference_tests():
+    """The parts of TestFilterbankClass (tests/test_audio_filters.py:709-833) that apply to the drop-in Filterbank (it
+    has no Filter / from_filters layer: banks are built directly): constructor types and errors, and the derived
+    properties on the reference's rectangular and triangular example banks written out as dense matrices."""
+    from madmom_b200.audio.filters import Filterbank, FILTER_DTYPE
+    filt = Filterbank(np.zeros((100, 10)), np.arange(100))
+    assert isinstance(filt, Filterbank) and filt.dtype == FILTER_DTYPE and filt.bin_frequencies.dtype == float
+    with pytest.raises(TypeError):
+        Filterbank(np.zeros((100, 10)))
+    with pytest.raises(TypeError):
+        Filterbank(np.zeros(10), np.arange(10))
+    with pytest.raises(ValueError):
+        Filterbank(np.zeros((100, 10)), np.arange(10))
+    rect = np.zeros((100, 4))
+    for b, (a, z) in enumerate(((0, 10), (10, 25), (25, 50), (50, 100))):
+        rect[a:z, b] = 1
+    filt = Filterbank(rect, np.arange(100))
+    assert filt.num_bands == 4 and filt.num_bins == 100 and filt.fmin == 0 and filt.fmax == 99
+    assert np.allclose(filt.min(), 0) and np.allclose(filt.max(), 1)
+    assert np.allclose(filt.bin_frequencies, np.arange(100))
+    assert np.allclose(filt.corner_frequencies, [[0, 9], [10, 24], [25, 49], [50, 99]])
+    assert np.allclose(filt.center_frequencies, [4, 17, 37, 74])
+    tri = np.zeros((100, 4))                                   # TriangularFilter(start, center, stop), norm=False
+    for b, (a, c, z) in enumerate(((0, 6, 15), (6, 15, 25), (15, 25, 50), (25, 50, 70))):
+        tri[a:c, b] = np.linspace(0, 1, c - a, endpoint=False)
+        tri[c:z, b] = np.linspace(1, 0, z - c, endpoint=False)
+    filt = Filterbank(tri, np.arange(100))
+    assert filt.num_bands == 4 and filt.fmin == 1 and filt.fmax == 69
+    assert np.allclose(filt.corner_frequencies, [[1, 14], [7, 24], [16, 49], [26, 69]])
+    assert np.allclose(filt.center_frequencies, [6, 15, 25, 50])

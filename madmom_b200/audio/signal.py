@@ -83,6 +83,29 @@ def normalize(signal):
     return np.asanyarray(signal / scaling, dtype=signal.dtype)
 
 
+def smooth(signal, kernel):
+    """'same'-sized convolution of a 1-D signal, or of every channel of a 2-D one, with `kernel`: an array, or a
+    length > 1 for a Hamming window of that length; None or 0 leaves the signal as it is
+    (madmom/audio/signal.py:22-68; `peak_picking` smooths activations this way, on the device inside
+    mmb_peak_picking)."""
+    if kernel is None:
+        return signal
+    if isinstance(kernel, (int, np.integer)):
+        if kernel == 0:
+            return signal
+        if kernel < 2:
+            raise ValueError("can't create a smoothing kernel of size %d" % kernel)
+        kernel = np.hamming(kernel)
+    elif not (isinstance(kernel, np.ndarray) and kernel.ndim == 1 and len(kernel) > 1):
+        raise ValueError("can't smooth signal with %s" % (kernel,))
+    x = np.asarray(signal)
+    if x.ndim == 1:
+        return np.convolve(x, kernel, "same")
+    if x.ndim == 2:
+        return np.stack([np.convolve(x[:, c], kernel, "same") for c in range(x.shape[1])], axis=1)
+    raise ValueError("signal must be either 1D or 2D")
+
+
 def trim(signal, where="fb"):
     """Cut leading ('f') and / or trailing ('b') sample frames in which every channel is zero
     (madmom/audio/signal.py:295-329)."""

@@ -688,3 +688,29 @@ def test_filterbank_base_class_like_the_reference_tests():
     assert filt.num_bands == 4 and filt.fmin == 1 and filt.fmax == 69
     assert np.allclose(filt.corner_frequencies, [[1, 14], [7, 24], [16, 49], [26, 69]])
     assert np.allclose(filt.center_frequencies, [6, 15, 25, 50])
+
+
+def test_smooth_like_the_reference_tests():
+    """TestSmoothFunction, tests/test_audio_signal.py:27-93."""
+    from madmom_b200.audio.signal import smooth
+    sig_1d = np.asarray([0, 0, 1, 0, 0, 1, 0, 0, 1], dtype=float)
+    sig_2d = np.asarray([[0, 0, 1, 0, 0, 1, 0, 0, 1], [1, 0, 1, 0, 1, 0, 1, 0, 1]], dtype=float).T
+    for x in (sig_1d, sig_2d):
+        for k in (None, 3):
+            r = smooth(x, k)
+            assert type(r) == type(x) and r.shape == x.shape
+    for bad in ((np.zeros(9).reshape(3, 3), -1), (np.zeros(9).reshape(3, 3), "bla"), (np.zeros(18).reshape(3, 3, 2), 4)):
+        with pytest.raises(ValueError):
+            smooth(*bad)
+    assert np.allclose(smooth(sig_1d, None), sig_1d) and np.allclose(smooth(sig_1d, 0), sig_1d)
+    r3 = [0, 0.08, 1, 0.08, 0.08, 1, 0.08, 0.08, 1]
+    r5 = [0.08, 0.54, 1, 0.62, 0.62, 1, 0.62, 0.62, 1]
+    r7 = [0.31, 0.77, 1.08, 1.08, 1.08, 1.16, 1.08, 1.08, 1.08]
+    assert np.allclose(smooth(sig_1d, 3), r3) and np.allclose(smooth(sig_1d, 5), r5)
+    assert np.allclose(smooth(sig_1d, 7), r7)
+    assert np.allclose(smooth(sig_1d, np.ones(3)), [0, 1, 1, 1, 1, 1, 1, 1, 1])
+    assert np.allclose(smooth(sig_1d, np.ones(4)), [0, 1, 1, 1, 2, 1, 1, 2, 1])
+    assert np.allclose(smooth(sig_2d, None), sig_2d)
+    assert np.allclose(smooth(sig_2d, 3), np.asarray([r3, [1, 0.16, 1, 0.16, 1, 0.16, 1, 0.16, 1]]).T)
+    assert np.allclose(smooth(sig_2d, 5), np.asarray([r5, [1.08, 1.08, 1.16, 1.08, 1.16, 1.08, 1.16, 1.08, 1.08]]).T)
+    assert np.allclose(smooth(sig_2d, 7), np.asarray([r7, [1.31, 1.62, 1.62, 1.7, 1.62, 1.7, 1.62, 1.62, 1.31]]).T)

@@ -714,3 +714,33 @@ def test_smooth_like_the_reference_tests():
     assert np.allclose(smooth(sig_2d, 3), np.asarray([r3, [1, 0.16, 1, 0.16, 1, 0.16, 1, 0.16, 1]]).T)
     assert np.allclose(smooth(sig_2d, 5), np.asarray([r5, [1.08, 1.08, 1.16, 1.08, 1.16, 1.08, 1.16, 1.08, 1.08]]).T)
     assert np.allclose(smooth(sig_2d, 7), np.asarray([r7, [1.31, 1.62, 1.62, 1.7, 1.62, 1.7, 1.62, 1.62, 1.31]]).T)
+
+
+def test_stft_module_functions_like_the_reference_tests():
+    """TestBinFrequenciesFunction, TestPhaseFunction, TestLocalGroupDelayFunction (tests/test_audio_stft.py:23-44,
+    107-148) on the host utilities of the drop-in module.  The generic `stft()` of the reference (any frame size, on
+    the host) is deliberately not offered: a CPU transform in this package would be a CPU fallback."""
+    from madmom_b200.audio import stft as ST
+    for args in ((), (1,), (1, 2, 3)):
+        with pytest.raises(TypeError):
+            ST.fft_frequencies(*args)
+    r = ST.fft_frequencies(5, 10)
+    assert isinstance(r, np.ndarray) and r.dtype == float and np.allclose(r, [0, 1, 2, 3, 4])
+    assert not hasattr(ST, "stft")
+    rng = np.random.default_rng(0)
+    for shape in ((10,), (10, 2)):
+        r = ST.phase(rng.random(shape))
+        assert r.dtype == float and r.shape == shape
+        data = rng.random(shape) + 1j * rng.random(shape)
+        r = ST.phase(data)
+        assert r.dtype == float and r.shape == shape and np.allclose(np.angle(data), r)
+    r = ST.local_group_delay(rng.random((10, 2)))
+    assert r.dtype == float and r.shape == (10, 2)
+    with pytest.raises(ValueError):
+        ST.local_group_delay(np.arange(10))
+    with pytest.raises(ValueError):
+        ST.local_group_delay(np.arange(20).reshape(5, 2, 2))
+    assert np.allclose(np.tile([-2, 0], 10).reshape(10, 2), ST.local_group_delay(np.arange(20).reshape(10, 2) * 2))
+    assert np.allclose(np.tile([2.28318531, 0], 10).reshape(10, 2),
+                       ST.local_group_delay(np.arange(20).reshape(10, 2) * 4))
+    assert ST.lgd is ST.local_group_delay

@@ -34,6 +34,14 @@ DIFF_MAX_BINS = None
 POSITIVE_DIFFS = False
 
 
+def spec(stft):
+    """Magnitudes of a complex STFT, np.abs (madmom/audio/spectrogram.py:22-38).  A device STFT stays on the device
+    (the `Spectrogram` class); a plain array is answered on the host like `stft.phase()` does."""
+    if isinstance(stft, ShortTimeFourierTransform):
+        return Spectrogram(stft)
+    return np.abs(stft)
+
+
 class Spectrogram(DeviceResult):
     """Magnitude spectrogram |STFT|, (num_frames, num_bins) float32.
 

@@ -744,3 +744,15 @@ def test_stft_module_functions_like_the_reference_tests():
     assert np.allclose(np.tile([2.28318531, 0], 10).reshape(10, 2),
                        ST.local_group_delay(np.arange(20).reshape(10, 2) * 4))
     assert ST.lgd is ST.local_group_delay
+
+
+def test_spec_function_like_the_reference_tests():
+    """TestSpecFunction, tests/test_audio_spectrogram.py:44-67."""
+    from madmom_b200.audio.spectrogram import spec
+    rng = np.random.default_rng(1)
+    for shape in ((10,), (10, 2)):
+        r = spec(rng.random(shape))
+        assert r.dtype == float and r.shape == shape
+        data = rng.random(shape) + 1j * rng.random(shape)
+        r = spec(data)
+        assert r.dtype == float and r.shape == shape and np.allclose(np.abs(data), r)

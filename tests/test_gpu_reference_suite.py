@@ -54,6 +54,8 @@ def test_spectrogram_class(sig, fft_freqs):
     assert isinstance(result.diff(), SpectrogramDifference)
     assert isinstance(result.filter(), FilteredSpectrogram)
     assert isinstance(result.log(), LogarithmicSpectrogram)
+    from madmom_b200.audio.spectrogram import spec              # the module function keeps a device STFT on the device
+    assert isinstance(spec(ShortTimeFourierTransform(sig)), Spectrogram)
 
 
 def test_spectrogram_processor_class(sig, fft_freqs):

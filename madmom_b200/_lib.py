@@ -32,6 +32,7 @@ class Track(ctypes.Structure):
 
 TRACK_DTYPE = np.dtype([("pcm_offset", "<i8"), ("pcm_len", "<i8"), ("sample_base", "<i8"), ("frame_first", "<i8"),
                         ("frame_count", "<i8"), ("out_row", "<i8")])
+_UNIT_FIELD = {name: i for i, name in enumerate(TRACK_DTYPE.names)}
 
 
 class Outputs(ctypes.Structure):
@@ -259,6 +260,16 @@ class FrontEndPlan(object):
     def _check_extents(units, pcm_elems, out_rows):
         """The unit table must stay inside the tensors handed in: the kernel trusts it."""
         if len(units) == 0:
+            return
+        if len(units) == 1:                                  # one file at a time: no numpy temporaries (latency path)
+            u = units[0].item()                              # one tuple of Python ints
+            need_pcm = u[_UNIT_FIELD["pcm_offset"]] + u[_UNIT_FIELD["pcm_len"]]
+            need_rows = u[_UNIT_FIELD["out_row"]] + u[_UNIT_FIELD["frame_count"]]
+            if need_pcm > pcm_elems:
+                raise ValueError("unit table reads %d PCM samples, the pcm tensor has %d" % (need_pcm, pcm_elems))
+            for name, rows in out_rows.items():
+                if rows < need_rows:
+                    raise ValueError("output %r has %d rows, the unit table writes %d" % (name, rows, need_rows))
             return
         need_pcm = int((units["pcm_offset"] + units["pcm_len"]).max())
         if need_pcm > pcm_elems:

@@ -489,6 +489,20 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
           const S* xb = haveB ? span0 + (int)(frame_start_sample(gA + 1, p.hop, N, p.origin) - s_begin) : nullptr;
           load_frames_1024<S>(lane, v, xa, xb, s_win);
         }
+        // The two frames share one complex FFT, and the split separates them only up to rounding: a frame carries
+        // about 1e-7 of its partner's bins.  Between frames of music that is nothing, but a frame that is exactly
+        // silent after windowing (zero padding, digital silence, the all-but-one-sample first frame of an online
+        // framing under a window whose last tap is 0) must read exactly 0 like in the reference, which transforms
+        // every frame on its own.  So: which of the two frames has no non-zero sample?  (Depends on the frame's own
+        // samples only: rows stay independent of chunking and sharding.)
+        bool silentA, silentB;
+        {
+          unsigned bitsA = 0, bitsB = 0;
+#pragma unroll
+          for (int m = 0; m < 32; ++m) { bitsA |= __float_as_uint(v[m].x); bitsB |= __float_as_uint(v[m].y); }
+          silentA = __all_sync(0xffffffffu, (bitsA << 1) == 0);         // the sign of a zero does not count
+          silentB = __all_sync(0xffffffffu, (bitsB << 1) == 0);         // true when there is no frame B
+        }
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
         core_pass1(lane, v, ex, s_tw1);
         __syncwarp();
@@ -506,7 +520,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         }
         if (nb > 0) {
           __syncwarp();
-          if (!haveB) for (int i = lane; i < 512; i += 32) my_mag[512 + i] = 0.0f;
+          if (silentA) for (int i = lane; i < 512; i += 32) my_mag[i] = 0.0f;
+          if (silentB) for (int i = lane; i < 512; i += 32) my_mag[512 + i] = 0.0f;
           __syncwarp();
           warp_filterbank<2>(p, lane, my_mag, my_mag + 512, my_part, s_pass, s_w, s_start, s_pid);
           MMB_PENDING_DIFFERENCE();

@@ -15,6 +15,7 @@
 
 #include "../../include/madmom_b200.h"
 #include "frontend_params.h"
+#include "work_list.h"
 #include "fft_core.cuh"          // tw1_index: layout of the inter-pass twiddle table
 
 using mmb::FrontendParams;
@@ -58,6 +59,7 @@ struct Slot {
   void* d_out[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; size_t out_cap[7] = {0, 0, 0, 0, 0, 0, 0};
   Track* d_tracks = nullptr; size_t tracks_cap = 0;
   int32_t* d_prefix = nullptr; size_t prefix_cap = 0;
+  mmb::Chunk* d_work = nullptr; size_t work_cap = 0;
 };
 
 static cudaError_t ensure(void** p, size_t* cap, size_t need) {
@@ -77,7 +79,7 @@ struct HostPipe {
 void free_slots(Slot* slots, int n) {
   for (int s = 0; s < n; ++s) {
     if (slots[s].stream) { cudaStreamSynchronize(slots[s].stream); cudaStreamDestroy(slots[s].stream); }
-    cudaFree(slots[s].d_pcm); cudaFree(slots[s].d_raw); cudaFree(slots[s].d_tracks); cudaFree(slots[s].d_prefix);
+    cudaFree(slots[s].d_pcm); cudaFree(slots[s].d_raw); cudaFree(slots[s].d_tracks); cudaFree(slots[s].d_prefix); cudaFree(slots[s].d_work);
     for (int k = 0; k < 7; ++k) cudaFree(slots[s].d_out[k]);
     slots[s] = Slot();
   }
@@ -110,10 +112,12 @@ struct mmb_plan {
 
 struct mmb_layout {
   Track* d_tracks = nullptr;
-  int32_t* d_prefix = nullptr;
+  int32_t* d_prefix = nullptr;    // float64 STFT kernel: prefix sum of the units' chunks of chunk_frames frames
   int32_t n = 0;
   int32_t total_chunks = 0;
-  int32_t chunk_frames = 0;   // output frames per chunk of this layout (pick_chunk_frames)
+  int32_t chunk_frames = 0;       // (pick_chunk_frames)
+  mmb::Chunk* d_work = nullptr;   // fused kernel: its work list (build_work) and the CTAs it is laid out for
+  int32_t n_work = 0, work_grid = 0;
   int64_t total_rows = 0;
   int64_t pcm_extent = 0;     // max over units of pcm_offset + pcm_len
 };
@@ -413,10 +417,11 @@ static int validate_units(const mmb_track* u, int32_t n) {
   return MMB_OK;
 }
 
-// Output frames per chunk of one launch.  With plenty of work it is the plan's chunk (32 rounds: the lead-in frames
-// a chunk recomputes stay below 1 %).  A launch with fewer frames than that spreads over the SMs (one short file, the
-// drop-in use) gets the fewest rounds per chunk that still give every warp group at most one chunk, so the
-// latency is that of a few rounds instead of that of a whole chunk on one or two SMs.  Results do not depend on it.
+// Output frames per chunk of the float64 STFT kernel (one CTA per chunk) for one launch.  With plenty of work it is
+// the plan's chunk (32 rounds).  A launch with fewer frames than that spreads over the SMs (one short file, the
+// drop-in use) gets the fewest rounds per chunk that still give every SM at most one chunk, so the latency is that
+// of a few frames instead of that of a whole chunk on one or two SMs.  Results do not depend on it.  (The fused
+// kernel has its own work list, build_work.)
 static int pick_chunk_frames(const mmb_plan* p, const mmb_track* u, int32_t n) {
   if (p->chunk_fixed) return p->chunk_frames;
   int64_t total = 0;
@@ -443,9 +448,21 @@ static void build_prefix(const mmb_plan* p, const mmb_track* u, int32_t n, int c
   *rows = r;
 }
 
+// Work list of the fused kernel for one launch (work_list.h).  A plan with a fixed chunk size
+// (mmb_plan_config::chunk_frames, MMB_CHUNK_ROUNDS) gets equal chunks in unit order, else every group equal rounds.
+static void build_work(const mmb_plan* p, const mmb_track* u, int32_t n, std::vector<mmb::Chunk>& out, int* grid) {
+  static_assert(sizeof(mmb_track) == sizeof(Track), "mmb_track and Track are the same record");
+  int64_t wave_rounds = 64;
+  if (const char* env = std::getenv("MMB_WAVE_ROUNDS")) wave_rounds = std::max(std::atoi(env), 0);      // experiments
+  mmb::build_work_list(p->cfg.frame_size, mmb::frames_per_round(p->cfg.frame_size, p->group_warps),
+                       p->warps / p->group_warps, p->num_sms, p->cfg.diff_frames, p->chunk_fixed ? p->chunk_frames : 0,
+                       wave_rounds,
+                       reinterpret_cast<const Track*>(u), n, out, grid);
+}
+
 extern "C" int mmb_layout_destroy(mmb_layout* l) {
   if (!l) return MMB_OK;
-  cudaFree(l->d_tracks); cudaFree(l->d_prefix);
+  cudaFree(l->d_tracks); cudaFree(l->d_prefix); cudaFree(l->d_work);
   delete l;
   return MMB_OK;
 }
@@ -471,6 +488,14 @@ extern "C" int mmb_layout_create(const mmb_plan* p, const mmb_track* units, int3
     mmb_layout_destroy(l);
     return cuda_fail(e, "layout upload");
   }
+  std::vector<mmb::Chunk> work;
+  int grid = 0;
+  build_work(p, units, n, work, &grid);
+  l->n_work = (int32_t)work.size(); l->work_grid = grid;
+  if (!work.empty() && (e = upload(&l->d_work, work)) != cudaSuccess) {
+    mmb_layout_destroy(l);
+    return cuda_fail(e, "layout upload");
+  }
   *out = l;
   return MMB_OK;
 }
@@ -491,9 +516,19 @@ static int check_outputs(const mmb_plan* p, const mmb_outputs* o) {
 
 // Launches of one call: the raw-spectrum outputs (stft, spec) come from the float64 kernel (stft64.cu), everything
 // behind the filterbank and the lgd rows from the fused FP32 kernel.  *n_launched counts the kernels started.
-static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_prefix, int32_t n, int32_t chunks,
-                  int chunk_frames, const void* pcm_dev, int64_t pcm_extent, const mmb_outputs* o, cudaStream_t stream,
+// The units of one launch on the device, cut for the two kernels.
+struct DeviceWork {
+  const Track* tracks; int32_t n;
+  const int32_t* prefix; int32_t chunks, chunk_frames;      // float64 STFT kernel: one CTA per chunk
+  const mmb::Chunk* work; int32_t n_work, grid;             // fused kernel (build_work)
+};
+
+static int launch(const mmb_plan* p, const DeviceWork& w, const void* pcm_dev, int64_t pcm_extent,
+                  const mmb_outputs* o, cudaStream_t stream,
                   int* n_launched, const mmb_outputs* extra = nullptr, int n_extra = 0, bool multicast = false) {
+  const Track* d_tracks = w.tracks;
+  const int32_t n = w.n, chunks = w.chunks, chunk_frames = w.chunk_frames;
+  const int32_t* d_prefix = w.prefix;
   if (chunks < 1) return MMB_OK;
   if (o->stft || o->spec) {
     mmb::Stft64Params sp;
@@ -511,10 +546,11 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
   }
   const bool band_out = o->filt || o->log || o->diff || o->odf;
   if (!band_out && !o->lgd) return MMB_OK;
+  if (w.n_work < 1 || w.grid < 1) return MMB_OK;
   FrontendParams fp;
   std::memset(&fp, 0, sizeof(fp));
-  fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunk_prefix = d_prefix; fp.n_tracks = n; fp.total_chunks = chunks;
-  fp.chunk_frames = chunk_frames; fp.hop = p->cfg.hop_size; fp.origin = p->cfg.origin; fp.span_cap = p->span_cap;
+  fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunks = w.work; fp.n_tracks = n; fp.total_chunks = w.n_work;
+  fp.hop = p->cfg.hop_size; fp.origin = p->cfg.origin; fp.span_cap = p->span_cap;
   fp.win = p->d_win; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
   fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only the lgd rows are wanted
   fp.n_passes = p->n_passes; fp.max_q = p->max_q; fp.b_pad = p->b_pad; fp.w_floats = p->w_floats;
@@ -539,13 +575,15 @@ static int launch(const mmb_plan* p, const Track* d_tracks, const int32_t* d_pre
     if (const char* env = std::getenv("MMB_GATHER_VEC")) ok = ok && std::atoi(env) != 0;      // experiments
     fp.gather_vec = ok ? 1 : 0;
   }
-  const int groups = p->warps / p->group_warps;
-  int grid = p->num_sms;                              // one persistent CTA per SM
-  if (grid > (chunks + groups - 1) / groups) grid = (chunks + groups - 1) / groups;
-  cudaError_t e = mmb::launch_frontend(p->cfg.frame_size, p->sample_bytes, fp, grid, p->smem_bytes, stream);
+  // one persistent CTA per SM, fewer for a launch of a few rounds: the work list is laid out for this grid
+  cudaError_t e = mmb::launch_frontend(p->cfg.frame_size, p->sample_bytes, fp, w.grid, p->smem_bytes, stream);
   if (e != cudaSuccess) return cuda_fail(e, "frontend kernel launch");
   if (n_launched) ++*n_launched;
   return MMB_OK;
+}
+
+static DeviceWork work_of(const mmb_layout* l) {
+  return DeviceWork{l->d_tracks, l->n, l->d_prefix, l->total_chunks, l->chunk_frames, l->d_work, l->n_work, l->work_grid};
 }
 
 extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_dev, const mmb_outputs* outs,
@@ -557,7 +595,7 @@ extern "C" int mmb_run(const mmb_plan* p, const mmb_layout* l, const void* pcm_d
   if (rc) return rc;
   ON_DEVICE(p->cfg.device);
   int nl = 0;
-  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, outs,
+  rc = launch(p, work_of(l), pcm_dev, l->pcm_extent, outs,
               (cudaStream_t)stream, &nl);
   if (launches) *launches = nl;
   return rc;
@@ -582,7 +620,7 @@ extern "C" int mmb_run_gather(const mmb_plan* p, const mmb_layout* l, const void
   }
   ON_DEVICE(p->cfg.device);
   int nl = 0;
-  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, &dsts[0],
+  rc = launch(p, work_of(l), pcm_dev, l->pcm_extent, &dsts[0],
               (cudaStream_t)stream, &nl, dsts + 1, n_dst - 1);
   if (launches) *launches = nl;
   return rc;
@@ -599,7 +637,7 @@ extern "C" int mmb_run_multicast(const mmb_plan* p, const mmb_layout* l, const v
     return fail(MMB_E_UNSUPPORTED, "mmb_run_multicast stores the band outputs log, diff and odf only");
   ON_DEVICE(p->cfg.device);
   int nl = 0;
-  rc = launch(p, l->d_tracks, l->d_prefix, l->n, l->total_chunks, l->chunk_frames, pcm_dev, l->pcm_extent, mc,
+  rc = launch(p, work_of(l), pcm_dev, l->pcm_extent, mc,
               (cudaStream_t)stream, &nl, nullptr, 0, true);
   if (launches) *launches = nl;
   return rc;
@@ -705,6 +743,7 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
   {
     std::vector<Track> tab;
     std::vector<int32_t> prefix;
+    std::vector<mmb::Chunk> work;
     int32_t i0 = 0;
     int g = 0;
     while (i0 < n) {
@@ -734,11 +773,14 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
       int64_t dummy;
       const int chunk_frames = pick_chunk_frames(p, reinterpret_cast<const mmb_track*>(tab.data()), i1 - i0);
       build_prefix(p, reinterpret_cast<const mmb_track*>(tab.data()), i1 - i0, chunk_frames, prefix, &dummy);
+      int work_grid = 0;
+      build_work(p, reinterpret_cast<const mmb_track*>(tab.data()), i1 - i0, work, &work_grid);
       size_t pcm_bytes = (size_t)(pcm1 - pcm0) * sb;
       if (pcm_bytes == 0) pcm_bytes = sb;
       CUS(ensure(&S.d_pcm, &S.pcm_cap, pcm_bytes));
       CUS(ensure((void**)&S.d_tracks, &S.tracks_cap, tab.size() * sizeof(Track)));
       CUS(ensure((void**)&S.d_prefix, &S.prefix_cap, prefix.size() * sizeof(int32_t)));
+      CUS(ensure((void**)&S.d_work, &S.work_cap, std::max<size_t>(work.size(), 1) * sizeof(mmb::Chunk)));
       mmb_outputs od;
       std::memset(&od, 0, sizeof(od));
       for (int k = 0; k < 7; ++k) {
@@ -754,6 +796,8 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
       od.lgd = hptr[6] ? (float*)S.d_out[6] : nullptr; od.ld_lgd = K;
       CUS(cudaMemcpyAsync(S.d_tracks, tab.data(), tab.size() * sizeof(Track), cudaMemcpyHostToDevice, S.stream));
       CUS(cudaMemcpyAsync(S.d_prefix, prefix.data(), prefix.size() * sizeof(int32_t), cudaMemcpyHostToDevice, S.stream));
+      if (!work.empty())
+        CUS(cudaMemcpyAsync(S.d_work, work.data(), work.size() * sizeof(mmb::Chunk), cudaMemcpyHostToDevice, S.stream));
       if (channels == 1) {
         CUS(cudaMemcpyAsync(S.d_pcm, (const char*)pcm_host + (size_t)pcm0 * sb, (size_t)(pcm1 - pcm0) * sb,
                             cudaMemcpyHostToDevice, S.stream));
@@ -771,8 +815,9 @@ static int run_host_impl(const mmb_plan* p, const mmb_track* units, int32_t n, c
       // pageable tab/prefix vectors are reused by the next group: the async copies above are staged
       // synchronously by the runtime for pageable memory, so this is safe.
       if (prefix.back() > 0) {
-        status = launch(p, S.d_tracks, S.d_prefix, (int32_t)tab.size(), prefix.back(), chunk_frames, S.d_pcm, pcm1 - pcm0, &od,
-                        S.stream, &n_launch);
+        const DeviceWork dw{S.d_tracks, (int32_t)tab.size(), S.d_prefix, prefix.back(), chunk_frames,
+                            S.d_work, (int32_t)work.size(), work_grid};
+        status = launch(p, dw, S.d_pcm, pcm1 - pcm0, &od, S.stream, &n_launch);
         if (status) goto done;
         for (int k = 0; k < 7; ++k) {
           if (!hptr[k]) continue;

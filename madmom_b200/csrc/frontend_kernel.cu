@@ -61,7 +61,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 
 // ---------------------------------------------------------------------------------------------- round cursor
 // One lane walks the rounds of its warp group; `d` is advanced to the round that follows.  Group `vid` of `vstride`
-// groups in the grid takes chunks vid, vid + vstride, ...
+// groups in the grid takes the chunks vid, vid + vstride, ... of the launch's work list (FrontendParams::chunks).
 template <int N, typename S>
 __device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, int fpr, int vid, int vstride) {
   const int lead = ((p.out_diff != nullptr) || (p.out_odf != nullptr)) ? p.diff_frames : 0;
@@ -78,15 +78,18 @@ __device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, in
     if (g0 >= d.gb) { chunk += vstride; new_chunk = true; }
   }
   if (new_chunk) {
-    if (chunk >= p.total_chunks) { d.nfr = 0; return; }
-    int lo = 0, hi = p.n_tracks;
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (p.chunk_prefix[mid] <= chunk) lo = mid; else hi = mid;
+    // the next entry of the work list that holds frames (holes: the lists of the groups differ in length)
+    Chunk c;
+    for (;;) {
+      if (chunk >= p.total_chunks) { d.nfr = 0; return; }
+      c = p.chunks[chunk];
+      if (c.frames > 0) break;
+      chunk += vstride;
     }
+    const int lo = c.unit;
     const Track tr = p.tracks[lo];
-    const long long a_loc = (long long)(chunk - p.chunk_prefix[lo]) * p.chunk_frames;
-    const long long b_loc = min(a_loc + (long long)p.chunk_frames, (long long)tr.frame_count);
+    const long long a_loc = c.first;
+    const long long b_loc = min(a_loc + (long long)c.frames, (long long)tr.frame_count);
     d.chunk = chunk; d.unit = lo;
     d.ga = tr.frame_first + a_loc; d.gb = tr.frame_first + b_loc;
     d.row0 = tr.out_row - tr.frame_first;
@@ -94,7 +97,7 @@ __device__ void next_round(const FrontendParams& p, RoundDesc& d, bool first, in
     d.sample_base = tr.sample_base;
     g0 = max(d.ga - (long long)lead, 0LL);
     // N = 1024 packs frames (2m, 2m + 1) into one FFT: pairing by the global frame index (one more lead-in frame when
-    // needed; chunk sizes are even, capi.cu) keeps a frame's bits independent of how its unit is cut into chunks
+    // needed; the host cuts in front of even frames, capi.cu) keeps a frame's bits independent of how its unit is cut
     if (N == 1024) g0 &= ~1LL;
   }
   d.g0 = g0;

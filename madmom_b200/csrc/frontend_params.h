@@ -2,19 +2,9 @@
 #pragma once
 #include <stdint.h>
 #include <cuda_runtime.h>
+#include "work_list.h"      // Track, Chunk
 
 namespace mmb {
-
-// One unit of independent work: a track (batch mode) or a frame range of a long signal (shard mode).
-// Mirrors mmb_track in include/madmom_b200.h.
-struct Track {
-  int64_t pcm_offset;    // element offset of local sample 0 inside the PCM buffer
-  int64_t pcm_len;       // number of local samples; anything outside reads as zero (signal.py:928-962)
-  int64_t sample_base;   // global sample index of local sample 0 (0 for whole tracks)
-  int64_t frame_first;   // global index of the first output frame
-  int64_t frame_count;   // number of output rows
-  int64_t out_row;       // first output row of this unit
-};
 
 // Per-warp filterbank schedule (built on the host, capi.cu): every band is cut into pieces; in pass p lane l
 // accumulates   sum_i mag[start[p][l] + i] * w[p][i][l],  i < iters[p]   (weights zero-padded to iters[p], stored
@@ -42,10 +32,9 @@ struct FrontendParams {
   int64_t pcm_extent;            // elements of the PCM buffer that may be read (max over units of offset + len)
   int32_t bulk_allowed;          // PCM base is 16-byte aligned: rounds may be staged with cp.async.bulk
   const Track* tracks;
-  const int32_t* chunk_prefix;   // [n_tracks + 1] prefix sum of chunks per track
+  const Chunk* chunks;           // [total_chunks] the work list of the launch; warp group v of V takes v, v + V, ...
   int32_t n_tracks;
   int32_t total_chunks;
-  int32_t chunk_frames;          // output frames per chunk
   double hop;                    // frame i starts at (int64)(i * hop) - N/2 - origin   (signal.py:917-919)
   int32_t origin;
   int32_t span_cap;              // capacity (samples) of one staged PCM span in shared memory

@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256, 4) stft64_kernel(const Stft64Params p) {
   float2* so = reinterpret_cast<float2*>(zs + M);              // [stft64_out_slots(M)] staged complex64 bins (out_slot)
   const int tid = threadIdx.x, nthreads = blockDim.x;
   const int chunk = (int)blockIdx.x;
-  // unit of this chunk (binary search in the prefix sums, like next_round() of the fused kernel)
+  // unit of this chunk (binary search in the prefix sums of the units' chunk counts)
   int lo = 0, hi = p.n_tracks;
   while (hi - lo > 1) {
     const int mid = (lo + hi) >> 1;

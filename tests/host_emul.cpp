@@ -85,3 +85,22 @@ extern "C" void emul_fft32(const float* re_in, const float* im_in, float* re_out
   fft32_dif(v);
   for (int r = 0; r < 32; ++r) { re_out[brev5(r)] = v[r].x; im_out[brev5(r)] = v[r].y; }
 }
+
+// ---------------------------------------------------------------------------------------------- work list
+// The host-side cut of a launch's units into the fused kernel's work list (madmom_b200/csrc/work_list.h), for
+// tests/test_host_logic.py.  units: n x 6 int64 (the mmb_track record).  Returns the number of entries written to
+// `out` (3 int64 each: unit, frames, first), -1 when `cap` entries do not hold them; *grid = CTAs of the launch.
+#include "../madmom_b200/csrc/work_list.h"
+
+extern "C" long long emul_work_list(int N, int fpr, int groups, int num_sms, long long lead, long long fixed_chunk,
+                                    long long wave_rounds, const long long* units, int n, long long* out, long long cap, int* grid) {
+  static_assert(sizeof(mmb::Track) == 6 * sizeof(long long), "Track is six int64");
+  std::vector<mmb::Chunk> work;
+  mmb::build_work_list(N, fpr, groups, num_sms, lead, fixed_chunk, wave_rounds, reinterpret_cast<const mmb::Track*>(units), n, work,
+                       grid);
+  if ((long long)work.size() > cap) return -1;
+  for (size_t k = 0; k < work.size(); ++k) {
+    out[3 * k] = work[k].unit; out[3 * k + 1] = work[k].frames; out[3 * k + 2] = work[k].first;
+  }
+  return (long long)work.size();
+}

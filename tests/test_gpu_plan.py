@@ -185,6 +185,24 @@ def test_rows_do_not_depend_on_chunking(N, ratio):
             assert np.array_equal(got[k], ref[k], equal_nan=True), (N, chunk, k)
 
 
+@pytest.mark.parametrize("N", [1024, 2048, 4096])
+def test_rows_do_not_depend_on_the_work_list(N, monkeypatch):
+    """The default cut (equal rounds per warp group, in waves: work_list.h) against fixed chunks, for a batch large
+    enough that every CTA gets several waves, with wave lengths that put the cuts everywhere."""
+    from madmom_b200.synth import make_track
+    rng = np.random.default_rng(N)
+    lens = [int(v) for v in rng.integers(1, 44100 * 12, 40)] + [0, 1, 441]
+    tracks = [make_track(3000 + i, num_samples=n) for i, n in enumerate(lens)]
+    plan, _ = _plan_for(np.int16, N, 441., 6, True, ratio=0.25, chunk_frames=50)
+    ref, _ = _run_all(plan, tracks, 441.)
+    for wave in ("0", "1", "3", "64"):
+        monkeypatch.setenv("MMB_WAVE_ROUNDS", wave)
+        plan, _ = _plan_for(np.int16, N, 441., 6, True, ratio=0.25)
+        got, _ = _run_all(plan, tracks, 441.)
+        for k in ("log", "diff", "odf"):
+            assert np.array_equal(got[k], ref[k], equal_nan=True), (N, wave, k)
+
+
 def test_float32_pcm(ref_synth):
     from oracle import frontend as O
     from madmom_b200.synth import make_track

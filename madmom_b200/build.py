@@ -11,8 +11,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIBPATH = os.path.join(LIBDIR, "libmadmom_b200.so")
-# (source, object name, extra flags): the front-end kernel is compiled once per frame size, in parallel
+# (source, object name, extra flags): the front-end kernel is compiled once per frame size and window path (table /
+# cosine sum evaluated in the kernel), in parallel
 SOURCES = [("frontend_kernel.cu", "frontend_kernel_%d.o" % n, ["-DMMB_FRONTEND_N=%d" % n]) for n in (2048, 4096, 1024)]
+SOURCES += [("frontend_kernel.cu", "frontend_kernel_%d_wcos.o" % n, ["-DMMB_FRONTEND_N=%d" % n, "-DMMB_FRONTEND_WCOS=1"])
+            for n in (2048, 4096)]
 SOURCES += [("frontend_dispatch.cu", "frontend_dispatch.o", ["-DMMB_SPLIT_FRONTEND"]), ("capi.cu", "capi.o", []),
             ("calibration.cu", "calibration.o", []), ("postproc.cu", "postproc.o", []),
             ("stft64.cu", "stft64.o", [])]

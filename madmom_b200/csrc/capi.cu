@@ -101,7 +101,8 @@ struct mmb_plan {
   int chunk_frames = 0;          // output frames per chunk of a launch with plenty of work (upper bound)
   bool chunk_fixed = false;      // set by the caller / MMB_CHUNK_ROUNDS: never adapted to the size of a launch
   int n_passes = 0, max_q = 0, b_pad = 0, w_floats = 0, fb_iters = 0;
-  float* d_win = nullptr;
+  float* d_win = nullptr;        // fft_window * 0.5 as float32, or the constants of a cosine-sum window (win_cos)
+  bool win_cos = false;
   double* d_win64 = nullptr;     // fft_window in float64 and W_N^k, k < N/2: the float64 STFT kernel (stft64.cu)
   double2* d_tw64 = nullptr;
   float2 *d_tw1 = nullptr, *d_tw2k = nullptr, *d_tw4k = nullptr;
@@ -254,6 +255,34 @@ void build_schedule(const mmb_config* cfg, int K, const std::vector<int32_t>& wo
 }
 }  // namespace
 
+// Is `w` (N float64 values) a symmetric cosine sum  a0 - a1 cos(2 pi n / (N - 1))  of any scale, to 1e-9 of its
+// peak?  Then `wc` gets the constants the kernel evaluates 0.5 w from (the 0.5 of the real-FFT split, like the table):
+// float4 l (l < 32): A = -0.5 a1 cos(t n), B = 0.5 a1 sin(t n) for n = 2 l and 2 l + 1 as (A, A', B, B');
+// float4 32 + l: the same for n + 2048 (N = 4096); float 256: 0.5 a0.
+static bool cosine_window_constants(const double* w, int N, std::vector<float>& wc) {
+  const double PI = 3.14159265358979323846264338327950288;
+  const double t = 2.0 * PI / (N - 1);
+  // a0 - a1 from n = 0, a0 - a1 cos(t N/2) from the middle
+  const double c_mid = std::cos(t * (N / 2));
+  const double a1 = (w[N / 2] - w[0]) / (1.0 - c_mid), a0 = w[0] + a1;
+  double peak = 0.0, worst = 0.0;
+  for (int n = 0; n < N; ++n) {
+    peak = std::max(peak, std::fabs(w[n]));
+    worst = std::max(worst, std::fabs(w[n] - (a0 - a1 * std::cos(t * n))));
+  }
+  if (!(peak > 0.0) || !(worst <= 1e-9 * peak) || !(std::fabs(a1) > 1e-6 * peak)) return false;
+  wc.assign(mmb::kWinCosFloats, 0.0f);
+  for (int half = 0; half < (N == 4096 ? 2 : 1); ++half)
+    for (int l = 0; l < 32; ++l)
+      for (int odd = 0; odd < 2; ++odd) {
+        const double n = 2 * l + odd + 2048 * half;
+        wc[(32 * half + l) * 4 + odd] = (float)(-0.5 * a1 * std::cos(t * n));
+        wc[(32 * half + l) * 4 + 2 + odd] = (float)(0.5 * a1 * std::sin(t * n));
+      }
+  wc[256] = (float)(0.5 * a0);
+  return true;
+}
+
 extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   NvtxRange nvtx_("mmb_plan_create");
   if (!cfg || !out) return fail(MMB_E_INVALID, "null argument");
@@ -303,6 +332,9 @@ extern "C" int mmb_plan_create(const mmb_config* cfg, mmb_plan** out) {
   const double PI = 3.14159265358979323846264338327950288;
   std::vector<float> win(N);
   for (int i = 0; i < N; ++i) win[i] = (float)(0.5 * cfg->fft_window[i]);
+  // a symmetric cosine-sum window (np.hanning, np.hamming, any scale) is evaluated in the kernel from a few
+  // constants instead of loaded (frame_fft.cuh: load_frame_2048_wcos); MMB_WIN_TABLE=1 keeps the table
+  p->win_cos = (N == 2048 || N == 4096) && !std::getenv("MMB_WIN_TABLE") && cosine_window_constants(cfg->fft_window, N, win);
   std::vector<float2> tw1(1024), tw2k(1024), tw4k(512);
   for (int k1 = 0; k1 < 32; ++k1)
     for (int l = 0; l < 32; ++l) {
@@ -551,7 +583,7 @@ static int launch(const mmb_plan* p, const DeviceWork& w, const void* pcm_dev, i
   std::memset(&fp, 0, sizeof(fp));
   fp.pcm = pcm_dev; fp.tracks = d_tracks; fp.chunks = w.work; fp.n_tracks = n; fp.total_chunks = w.n_work;
   fp.hop = p->cfg.hop_size; fp.origin = p->cfg.origin; fp.span_cap = p->span_cap;
-  fp.win = p->d_win; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
+  fp.win = p->d_win; fp.win_cos = p->win_cos ? 1 : 0; fp.tw1 = p->d_tw1; fp.tw2k = p->d_tw2k; fp.tw4k = p->d_tw4k;
   fp.n_bands = band_out ? p->cfg.num_bands : 0;     // skip phases B/C when only the lgd rows are wanted
   fp.n_passes = p->n_passes; fp.max_q = p->max_q; fp.b_pad = p->b_pad; fp.w_floats = p->w_floats;
   fp.fb_pass = p->d_pass; fp.fb_w = p->d_fbw; fp.fb_start = p->d_fbstart; fp.fb_pid = p->d_fbpid;

@@ -11,6 +11,9 @@
 // madmom/audio/stft.py:331-349).
 #pragma once
 #include "fft_core.cuh"
+#if defined(__CUDACC__)
+#include "win_cos_tables.h"
+#endif
 
 namespace mmb {
 
@@ -38,6 +41,32 @@ MMB_HD void load_frame_2048(int lane, float2 (&v)[32], const S* x, const float* 
     v[m] = mul2(make_float2(to_f32(x[2 * n]), to_f32(x[2 * n + 1])), w);
   }
 }
+
+// The same for a symmetric cosine-sum window w[n] = a0 - a1 cos(t n), t = 2 pi / (N - 1) (np.hanning, np.hamming;
+// capi.cu recognises them): at n = n0 + 64 m, n0 = 2 lane (+ 1),
+//   w = a0 - a1 cos(t n0) cos(64 t m) + a1 sin(t n0) sin(64 t m) = G + A C_m + B S_m
+// with the lane's A = -a1 cos(t n0), B = a1 sin(t n0) for its even and its odd sample (`wc`: 32 x float4
+// (A_even, A_odd, B_even, B_odd), G at float 256; capi.cu: cosine_window_constants) and C_m, S_m from the constant bank (win_cos_tables.h: uniform-register
+// operands).  Two packed FMAs per complex element instead of an 8-byte shared-memory load: the window loads are 64 of the
+// 663 shared-memory wavefronts of a frame and that pipe is the busiest unit of the kernel.
+// Each window value is within 3e-7 of the window's peak of the float32 table value.
+#if defined(__CUDACC__)
+template <typename S>
+__device__ __forceinline__ void load_frame_2048_wcos(int lane, float2 (&v)[32], const S* x,
+                                                     const float* __restrict__ wc) {
+  const float4 k = reinterpret_cast<const float4*>(wc)[lane];
+  const float G = wc[256];
+#pragma unroll
+  for (int m = 0; m < 32; ++m) {
+    const int n = lane + 32 * m;
+    const float C = kWinCos2048[m], Sn = kWinSin2048[m];
+    // two packed FMAs: (A, A') C_m + ((B, B') S_m + G), the scalars broadcast (FFMA2 R, R.F32x2, UR.F32, R.F32)
+    const float2 w = fma2(make_float2(k.x, k.y), make_float2(C, C),
+                          fma2(make_float2(k.z, k.w), make_float2(Sn, Sn), make_float2(G, G)));
+    v[m] = mul2(make_float2(to_f32(x[2 * n]), to_f32(x[2 * n + 1])), w);
+  }
+}
+#endif
 
 // two frames (xb may be null -> zero imaginary part)
 template <typename S>
@@ -68,6 +97,34 @@ MMB_HD void load_frame_4096(int lane, int c, float2 (&v)[32], const S* x, const 
     }
   }
 }
+
+// cosine-sum window (see load_frame_2048_wcos): `wc` holds 32 x float4 for the samples 2 n, 2 n + 1, 32 x float4 for
+// 2 n + 2048, 2 n + 2049, G at float 256
+#if defined(__CUDACC__)
+template <typename S>
+__device__ __forceinline__ void load_frame_4096_wcos(int lane, int c, float2 (&v)[32], const S* x,
+                                                     const float* __restrict__ wc,
+                                                     const float2* __restrict__ tw2k) {
+  const float4 k0 = reinterpret_cast<const float4*>(wc)[lane];
+  const float4 k1 = reinterpret_cast<const float4*>(wc)[32 + lane];
+  const float G = wc[256];
+#pragma unroll
+  for (int m = 0; m < 32; ++m) {
+    const int n = lane + 32 * m;
+    const float C = kWinCos4096[m], Sn = kWinSin4096[m];
+    const float2 cc = make_float2(C, C), ss = make_float2(Sn, Sn), gg = make_float2(G, G);
+    const float2 w0 = fma2(make_float2(k0.x, k0.y), cc, fma2(make_float2(k0.z, k0.w), ss, gg));
+    const float2 w1 = fma2(make_float2(k1.x, k1.y), cc, fma2(make_float2(k1.z, k1.w), ss, gg));
+    const float2 z0 = mul2(make_float2(to_f32(x[2 * n]), to_f32(x[2 * n + 1])), w0);
+    const float2 z1 = mul2(make_float2(to_f32(x[2 * n + 2048]), to_f32(x[2 * n + 2049])), w1);
+    if (c == 0) {
+      v[m] = add2(z0, z1);
+    } else {
+      v[m] = cmul(sub2(z0, z1), tw2k[m * 32 + lane]);
+    }
+  }
+}
+#endif
 
 // log(mul * x + add) with the reference's order of operations and roundings (x *= mul; x += add; log(x),
 // madmom/audio/spectrogram.py:527-534).  mode: 1 log10, 2 none (mul/add only), 3 ln, 4 log2.

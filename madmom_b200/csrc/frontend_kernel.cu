@@ -367,7 +367,8 @@ __device__ __forceinline__ void round_difference(const FrontendParams& p, const 
 // SPECOUT: per-bin outputs the launch may write: 0 none, 2 lgd (N = 2048): its own instantiation, so that launches
 // that only produce band outputs carry no emitting copy of the split.  (Raw bins and magnitudes -- the `stft` and
 // `spec` outputs -- come from the float64 kernel in stft64.cu, not from here.)
-template <int N, typename S, bool GATHER, int SPECOUT>
+// WCOS: the window is a symmetric cosine sum and is evaluated instead of loaded (frame_fft.cuh; N = 2048, 4096)
+template <int N, typename S, bool GATHER, int SPECOUT, bool WCOS>
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const FrontendParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   constexpr int K = N / 2;
@@ -402,7 +403,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
                                       : reinterpret_cast<float*>(smem + L.part + (warp / part_sharers(N)) * L.part_stride);
 
   // ---- plan constants -> shared memory (once per persistent CTA)
-  for (int i = tid; i < N; i += nthreads) s_win[i] = p.win[i];
+  for (int i = tid; i < (WCOS ? kWinCosFloats : N); i += nthreads) s_win[i] = p.win[i];
   for (int i = tid; i < 1024; i += nthreads) s_tw1[i] = p.tw1[i];
   if (N == 2048) for (int i = tid; i < 512; i += nthreads) s_tw2k[i] = p.tw2k[i];
   if (N == 4096) {
@@ -548,7 +549,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
       } else {
         const S* x = span0 + (int)(frame_start_sample(D->g0 + f, p.hop, N, p.origin) - D->s_begin);
-        load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
+        if (WCOS) load_frame_4096_wcos<S>(lane, c, v, x, s_win, s_tw2k);
+        else load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
         core_pass1(lane, v, ex, s_tw1);
         __syncwarp();
@@ -577,7 +579,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     } else {
       const S* x = span0 + (int)(frame_start_sample(D->g0 + gwarp, p.hop, N, p.origin) - D->s_begin);
       {
-        load_frame_2048<S>(lane, v, x, s_win);
+        if (WCOS) load_frame_2048_wcos<S>(lane, v, x, s_win);
+        else load_frame_2048<S>(lane, v, x, s_win);
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
         core_pass1(lane, v, ex, s_tw1);
         __syncwarp();
@@ -613,74 +616,81 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
 }
 
 // ---------------------------------------------------------------------------------------------- host launchers
-template <int N, typename S>
+template <int N, typename S, bool WCOS>
 static cudaError_t launch_one(const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
   const bool lgd = p.out_lgd != nullptr;
   const int threads = p.warps * 32;
-  if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true, 0><<<grid, threads, smem_bytes, stream>>>(p);
-  else if (N == 2048 && lgd) frontend_kernel<N, S, false, (N == 2048 ? 2 : 0)><<<grid, threads, smem_bytes, stream>>>(p);
-  else frontend_kernel<N, S, false, 0><<<grid, threads, smem_bytes, stream>>>(p);
+  if (p.n_extra > 0 || p.multicast) frontend_kernel<N, S, true, 0, WCOS><<<grid, threads, smem_bytes, stream>>>(p);
+  else if (N == 2048 && lgd) frontend_kernel<N, S, false, (N == 2048 ? 2 : 0), WCOS><<<grid, threads, smem_bytes, stream>>>(p);
+  else frontend_kernel<N, S, false, 0, WCOS><<<grid, threads, smem_bytes, stream>>>(p);
   return cudaGetLastError();
 }
 
-#if defined(MMB_FRONTEND_N)
-// One frame size per translation unit (madmom_b200/build.py compiles this file three times in parallel with
-// -DMMB_FRONTEND_N=1024 / 2048 / 4096; frontend_dispatch.cu routes launch_frontend / frontend_set_smem to them).
-#define MMB_CAT2(a, b) a##b
-#define MMB_CAT(a, b) MMB_CAT2(a, b)
-cudaError_t MMB_CAT(launch_frontend_, MMB_FRONTEND_N)(int sample_bytes, const FrontendParams& p, int grid,
-                                                      int smem_bytes, cudaStream_t stream) {
-  if (sample_bytes == 2) return launch_one<MMB_FRONTEND_N, int16_t>(p, grid, smem_bytes, stream);
-  if (sample_bytes == 4) return launch_one<MMB_FRONTEND_N, float>(p, grid, smem_bytes, stream);
+template <int N, typename S, bool WCOS>
+static cudaError_t set_one(int smem_bytes) {
+  const cudaFuncAttribute a = cudaFuncAttributeMaxDynamicSharedMemorySize;
+  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false, 0, WCOS>, a, smem_bytes);
+  if (e == cudaSuccess && N == 2048)
+    e = cudaFuncSetAttribute(frontend_kernel<N, S, false, (N == 2048 ? 2 : 0), WCOS>, a, smem_bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<N, S, true, 0, WCOS>, a, smem_bytes);
+  return e;
+}
+
+template <int N, bool WCOS>
+static cudaError_t launch_n(int sample_bytes, const FrontendParams& p, int grid, int smem_bytes, cudaStream_t stream) {
+  if (sample_bytes == 2) return launch_one<N, int16_t, WCOS>(p, grid, smem_bytes, stream);
+  if (sample_bytes == 4) return launch_one<N, float, WCOS>(p, grid, smem_bytes, stream);
   return cudaErrorInvalidValue;
+}
+template <int N, bool WCOS>
+static cudaError_t set_n(int sample_bytes, int smem_bytes) {
+  if (sample_bytes == 2) return set_one<N, int16_t, WCOS>(smem_bytes);
+  if (sample_bytes == 4) return set_one<N, float, WCOS>(smem_bytes);
+  return cudaErrorInvalidValue;
+}
+
+#if defined(MMB_FRONTEND_N)
+// One frame size and one window path per translation unit (madmom_b200/build.py compiles this file once per
+// (N, WCOS) in parallel with -DMMB_FRONTEND_N=1024 / 2048 / 4096 -DMMB_FRONTEND_WCOS=0 / 1; frontend_dispatch.cu
+// routes launch_frontend / frontend_set_smem to them).
+#if !defined(MMB_FRONTEND_WCOS)
+#define MMB_FRONTEND_WCOS 0
+#endif
+#define MMB_CAT3(a, b, c) a##b##c
+#define MMB_CAT(a, b, c) MMB_CAT3(a, b, c)
+#if MMB_FRONTEND_WCOS
+#define MMB_UNIT_SUFFIX _wcos
+#else
+#define MMB_UNIT_SUFFIX
+#endif
+cudaError_t MMB_CAT(launch_frontend_, MMB_FRONTEND_N, MMB_UNIT_SUFFIX)(int sample_bytes, const FrontendParams& p,
+                                                                        int grid, int smem_bytes,
+                                                                        cudaStream_t stream) {
+  return launch_n<MMB_FRONTEND_N, MMB_FRONTEND_WCOS != 0>(sample_bytes, p, grid, smem_bytes, stream);
+}
+cudaError_t MMB_CAT(frontend_set_smem_, MMB_FRONTEND_N, MMB_UNIT_SUFFIX)(int sample_bytes, int smem_bytes) {
+  return set_n<MMB_FRONTEND_N, MMB_FRONTEND_WCOS != 0>(sample_bytes, smem_bytes);
 }
 #else
 cudaError_t launch_frontend(int N, int sample_bytes, const FrontendParams& p, int grid, int smem_bytes,
                             cudaStream_t stream) {
-  if (sample_bytes == 2) {
-    if (N == 1024) return launch_one<1024, int16_t>(p, grid, smem_bytes, stream);
-    if (N == 2048) return launch_one<2048, int16_t>(p, grid, smem_bytes, stream);
-    if (N == 4096) return launch_one<4096, int16_t>(p, grid, smem_bytes, stream);
-  } else if (sample_bytes == 4) {
-    if (N == 1024) return launch_one<1024, float>(p, grid, smem_bytes, stream);
-    if (N == 2048) return launch_one<2048, float>(p, grid, smem_bytes, stream);
-    if (N == 4096) return launch_one<4096, float>(p, grid, smem_bytes, stream);
-  }
+  const bool wcos = p.win_cos != 0;
+  if (N == 1024 && !wcos) return launch_n<1024, false>(sample_bytes, p, grid, smem_bytes, stream);
+  if (N == 2048) return wcos ? launch_n<2048, true>(sample_bytes, p, grid, smem_bytes, stream)
+                             : launch_n<2048, false>(sample_bytes, p, grid, smem_bytes, stream);
+  if (N == 4096) return wcos ? launch_n<4096, true>(sample_bytes, p, grid, smem_bytes, stream)
+                             : launch_n<4096, false>(sample_bytes, p, grid, smem_bytes, stream);
   return cudaErrorInvalidValue;
 }
 
-#endif
-
-template <int N, typename S>
-static cudaError_t set_one(int smem_bytes) {
-  const cudaFuncAttribute a = cudaFuncAttributeMaxDynamicSharedMemorySize;
-  cudaError_t e = cudaFuncSetAttribute(frontend_kernel<N, S, false, 0>, a, smem_bytes);
-  if (e == cudaSuccess && N == 2048) e = cudaFuncSetAttribute(frontend_kernel<N, S, false, (N == 2048 ? 2 : 0)>, a, smem_bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(frontend_kernel<N, S, true, 0>, a, smem_bytes);
-  return e;
-}
-
-#if defined(MMB_FRONTEND_N)
-cudaError_t MMB_CAT(frontend_set_smem_, MMB_FRONTEND_N)(int sample_bytes, int smem_bytes) {
-  if (sample_bytes == 2) return set_one<MMB_FRONTEND_N, int16_t>(smem_bytes);
-  if (sample_bytes == 4) return set_one<MMB_FRONTEND_N, float>(smem_bytes);
-  return cudaErrorInvalidValue;
-}
-#else
-// opt the kernel variant in to `smem_bytes` of dynamic shared memory (once per plan)
+// opt the kernel variants in to `smem_bytes` of dynamic shared memory (once per plan)
 cudaError_t frontend_set_smem(int N, int sample_bytes, int smem_bytes) {
-  if (sample_bytes == 2) {
-    if (N == 1024) return set_one<1024, int16_t>(smem_bytes);
-    if (N == 2048) return set_one<2048, int16_t>(smem_bytes);
-    if (N == 4096) return set_one<4096, int16_t>(smem_bytes);
-  } else if (sample_bytes == 4) {
-    if (N == 1024) return set_one<1024, float>(smem_bytes);
-    if (N == 2048) return set_one<2048, float>(smem_bytes);
-    if (N == 4096) return set_one<4096, float>(smem_bytes);
-  }
-  return cudaErrorInvalidValue;
+  if (N == 1024) return set_n<1024, false>(sample_bytes, smem_bytes);
+  cudaError_t e = N == 2048 ? set_n<2048, false>(sample_bytes, smem_bytes)
+                : N == 4096 ? set_n<4096, false>(sample_bytes, smem_bytes) : cudaErrorInvalidValue;
+  if (e != cudaSuccess) return e;
+  return N == 2048 ? set_n<2048, true>(sample_bytes, smem_bytes) : set_n<4096, true>(sample_bytes, smem_bytes);
 }
-
 #endif
 
 }  // namespace mmb

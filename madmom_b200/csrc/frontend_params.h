@@ -25,6 +25,7 @@ struct SmemLayout {
   int pcm_stride;        // bytes of staged PCM span per warp group
 };
 
+constexpr int kWinCosFloats = 260;   // cosine-sum window constants: 2 x 32 float4 per-lane factors, then a0 (258 used)
 constexpr int kMaxExtraDst = 7;      // destinations of one launch besides the local one (8 GPUs of a node)
 
 struct FrontendParams {
@@ -42,7 +43,8 @@ struct FrontendParams {
   int32_t group_warps;           // warps per group; a group walks its own chunks in rounds of frames_per_round frames
   SmemLayout L;
   // plan constants (device)
-  const float* win;              // N floats, fft_window * 0.5
+  const float* win;              // N floats, fft_window * 0.5; win_cos: the constants of frame_fft.cuh's *_wcos loads
+  int32_t win_cos;               // the window is a symmetric cosine sum, evaluated in the kernel (N = 2048, 4096)
   const float2* tw1;             // 1024: W1024^(l*k1) at [tw1_index(k1, l)] (fft_core.cuh)
   const float2* tw2k;            // 1024: W2048^k (N = 2048 uses the first 512)
   const float2* tw4k;            // 512 : W4096^(2j+1)

@@ -203,6 +203,64 @@ def test_rows_do_not_depend_on_the_work_list(N, monkeypatch):
             assert np.array_equal(got[k], ref[k], equal_nan=True), (N, wave, k)
 
 
+def _window_case(N, window, x, monkeypatch=None, table=False):
+    """log / diff / odf of `x` for frame size N and the window array, from the library and from the oracle."""
+    from oracle import frontend as O
+    from madmom_b200 import _lib
+    if monkeypatch is not None:
+        if table:
+            monkeypatch.setenv("MMB_WIN_TABLE", "1")
+        else:
+            monkeypatch.delenv("MMB_WIN_TABLE", raising=False)
+    fw = O.fft_window(window, N, x.dtype)
+    fb = O.logarithmic_filterbank(O.fft_frequencies(N // 2, 44100), 12, 30., 17000., 440., False, True)
+    plan = _lib.FrontEndPlan(N, 441., fw, pcm_dtype=x.dtype, filterbank=fb, log_mode=_lib.LOG_LOG10, mul=1., add=1.,
+                             diff_frames=1, diff_max_bins=0, positive_diffs=True)
+    got, _ = _run_all(plan, [x], 441.)
+    st = O.stft(O.framed(x, N, 441.), fw)
+    log = O.logarithmic(O.filtered(O.spec(st), fb), 1., 1.)
+    diff = O.difference(log, 1, None, True)
+    return got, {"log": log, "diff": diff, "odf": O.flux(diff)}
+
+
+@pytest.mark.parametrize("N", [2048, 4096])
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+def test_cosine_sum_windows_are_evaluated_in_the_kernel(N, dtype, monkeypatch):
+    """np.hanning / np.hamming (any scale) are recognised at plan creation and evaluated in the kernel instead of
+    loaded (frame_fft.cuh: *_wcos): against the oracle within the feature bound, and against the table path
+    (MMB_WIN_TABLE=1) far inside it (4e-6 per band) -- a window value moves by at most 3e-7 of the window's peak."""
+    from madmom_b200.synth import make_track
+    x = make_track(77, 2.0, dtype=dtype)
+    for window in (np.hanning(N), np.hamming(N), 3.5 * np.hanning(N), 0.25 - 0.75 * np.cos(2 * np.pi * np.arange(N) / (N - 1))):
+        got, ref = _window_case(N, window, x, monkeypatch, table=False)
+        tab, _ = _window_case(N, window, x, monkeypatch, table=True)
+        for k in ("log", "diff", "odf"):
+            assert_close(got[k], ref[k], what="cosine-sum window N=%d %s" % (N, k))
+            assert_close(tab[k], ref[k], what="table window N=%d %s" % (N, k))
+            err = np.abs(got[k].astype(np.float64) - tab[k].astype(np.float64))
+            bands = tab["log"].shape[1]
+            bound = 4e-6 * (bands if k == "odf" else 1) + 4e-6 * np.abs(tab[k].astype(np.float64))
+            assert (err <= bound).all(), (N, k, float(err.max()))
+        assert not np.array_equal(got["log"], tab["log"])          # two paths indeed
+
+
+@pytest.mark.parametrize("N", [2048, 4096])
+def test_other_windows_keep_the_table(N, monkeypatch):
+    """Windows that are not a cosine sum of the symmetric kind (Blackman, the periodic Hann, a rectangle, a Hann
+    with one tap off by 1e-6) go through the table: same bits with and without MMB_WIN_TABLE, oracle bound met."""
+    from madmom_b200.synth import make_track
+    x = make_track(78, 1.5)
+    n = np.arange(N)
+    bumped = np.hanning(N)
+    bumped[N // 3] += 1e-6
+    for window in (np.blackman(N), 0.5 - 0.5 * np.cos(2 * np.pi * n / N), np.ones(N), bumped):
+        got, ref = _window_case(N, window, x, monkeypatch, table=False)
+        tab, _ = _window_case(N, window, x, monkeypatch, table=True)
+        for k in ("log", "diff", "odf"):
+            assert_close(got[k], ref[k], what="window N=%d %s" % (N, k))
+            assert np.array_equal(got[k], tab[k]), (N, k)
+
+
 def test_float32_pcm(ref_synth):
     from oracle import frontend as O
     from madmom_b200.synth import make_track

@@ -236,12 +236,11 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
 }
 
 void build_schedule(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, FbSchedule& best) {
-  static const int kCandidates[] = {8, 12, 16, 20, 24, 28, 32, 48, 64};
   int forced = 0;
   if (const char* env = std::getenv("MMB_FB_PIECE")) forced = std::atoi(env);
   bool have = false;
   int best_cost = 0;
-  for (int P : kCandidates) {
+  for (int P = 6; P <= 96; ++P) {                       // every piece length: a schedule takes microseconds
     if (forced > 0 && P != forced) continue;
     FbSchedule s;
     schedule_with(cfg, K, woff, P, s);

@@ -86,7 +86,12 @@ inline void build_work_list(int N, int fpr, int groups, int num_sms, int64_t lea
     const int64_t left = rounds_of(u[i].frame_count - a) + after[i + 1];
     const int64_t waves = wave_rounds > 0 ? std::max<int64_t>((left + slots * wave_rounds / 2) / (slots * wave_rounds), 1) : 1;
     int64_t budget = std::max((left + slots * waves - 1) / (slots * waves), min_budget);
-    if (waves > 1) { wave(budget); continue; }
+    if (waves > 1) {
+      const int32_t i_was = i;
+      const int64_t a_was = a;
+      wave(budget);
+      if (i != i_was || a != a_was) continue;               // (no progress: lead-in longer than the budget; finish below)
+    }
     // the last wave takes all that is left; its cuts add a round here and there: one or two more tries
     const int32_t i0 = i;
     const int64_t a0 = a;

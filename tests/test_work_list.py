@@ -157,3 +157,14 @@ def test_ten_hours_in_one_unit(emul):
     rounds = check(work, grid, 2048, 16, 1, 148, 1, [frames])
     assert grid == 148 and work[:, 1].sum() == frames and (np.diff(work[:, 2]) == work[:-1, 1]).all()
     assert rounds[:-1].max() - rounds[:-1].min() <= 1 and rounds[-1] <= rounds[0]
+
+
+@pytest.mark.parametrize("N,fpr,groups,lead", [(1024, 2, 16, 16), (4096, 1, 8, 16), (2048, 1, 16, 16), (1024, 2, 1, 1)])
+def test_lead_in_longer_than_a_round(emul, N, fpr, groups, lead):
+    """Single-warp groups: a round holds one or two frames and the lead-in of a cut is many rounds."""
+    counts = [200_000, 3, 77_777]
+    firsts = [1, 0, 12345]
+    work, grid = work_list(emul, N, fpr, groups, 148, lead, counts, firsts)
+    check(work, grid, N, fpr, groups, 148, lead, counts, firsts)
+    work, grid = work_list(emul, N, fpr, groups, 148, lead, counts, firsts, wave=0)
+    check(work, grid, N, fpr, groups, 148, lead, counts, firsts, wave=0)

@@ -126,6 +126,53 @@ __device__ __forceinline__ void load_frame_4096_wcos(int lane, int c, float2 (&v
 }
 #endif
 
+// N = 4096, the pair's loads shared.  Both halves of the pre-stage need every packed element of the frame,
+// z[n] + z[n + 1024] for one warp and (z[n] - z[n + 1024]) W2048^n for the other; instead of both warps loading,
+// converting and windowing all 4096 samples, warp c does so for the elements m = 16 c .. 16 c + 15 of every lane
+// (n = lane + 32 m), forms BOTH combinations, keeps its own and leaves the partner's in `mine` ([16][32] float2,
+// the lower 4 KB of its exchange tile, idle in this phase).  After the pair's barrier take_frame_4096_half() picks
+// up the other sixteen from the partner's tile.  Same operations on the same operands as load_frame_4096: the bits do
+// not change; each warp has half of the load phase, and the odd warp no longer carries all 32 twiddle products.
+#if defined(__CUDACC__)
+template <typename S, bool WCOS>
+__device__ __forceinline__ void load_frame_4096_half(int lane, int c, float2 (&v)[32], const S* x,
+                                                     const float* __restrict__ win,
+                                                     const float2* __restrict__ tw2k, float2* mine) {
+  float4 k0 = make_float4(0.f, 0.f, 0.f, 0.f), k1 = k0;
+  float G = 0.f;
+  if (WCOS) {
+    k0 = reinterpret_cast<const float4*>(win)[lane];
+    k1 = reinterpret_cast<const float4*>(win)[32 + lane];
+    G = win[256];
+  }
+#pragma unroll
+  for (int m = 0; m < 32; ++m) {
+    if ((m >> 4) != c) continue;                       // warp-uniform: the other half is the partner's
+    const int n = lane + 32 * m;
+    float2 w0, w1;
+    if (WCOS) {
+      const float C = kWinCos4096[m], Sn = kWinSin4096[m];
+      const float2 cc = make_float2(C, C), ss = make_float2(Sn, Sn), gg = make_float2(G, G);
+      w0 = fma2(make_float2(k0.x, k0.y), cc, fma2(make_float2(k0.z, k0.w), ss, gg));
+      w1 = fma2(make_float2(k1.x, k1.y), cc, fma2(make_float2(k1.z, k1.w), ss, gg));
+    } else {
+      w0 = *reinterpret_cast<const float2*>(win + 2 * n);
+      w1 = *reinterpret_cast<const float2*>(win + 2 * n + 2048);
+    }
+    const float2 z0 = mul2(make_float2(to_f32(x[2 * n]), to_f32(x[2 * n + 1])), w0);
+    const float2 z1 = mul2(make_float2(to_f32(x[2 * n + 2048]), to_f32(x[2 * n + 2049])), w1);
+    const float2 y0 = add2(z0, z1), y1 = cmul(sub2(z0, z1), tw2k[m * 32 + lane]);
+    if (m < 16) { v[m] = y0; mine[(m & 15) * 32 + lane] = y1; }      // executed by warp c = 0 only
+    else { v[m] = y1; mine[(m & 15) * 32 + lane] = y0; }            // executed by warp c = 1 only
+  }
+}
+__device__ __forceinline__ void take_frame_4096_half(int lane, int c, float2 (&v)[32], const float2* theirs) {
+#pragma unroll
+  for (int m = 0; m < 32; ++m)
+    if ((m >> 4) != c) v[m] = theirs[(m & 15) * 32 + lane];
+}
+#endif
+
 // log(mul * x + add) with the reference's order of operations and roundings (x *= mul; x += add; log(x),
 // madmom/audio/spectrogram.py:527-534).  mode: 1 log10, 2 none (mul/add only), 3 ln, 4 log2.
 MMB_HD float log_scaled(float x, int mode, float mul, float add) {

@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
     } else if (N == 4096) {
       // two warps per frame: the radix-2 pre-stage splits the packed 2048-point sequence into the half that gives the
       // even bins (warp 2f, c = 0) and the one that gives the odd bins (warp 2f + 1, c = 1); each is a 1024-point
-      // complex FFT of its own.  The pair meets twice: before the filterbank (both magnitude arrays are in place;
+      // complex FFT of its own.  The pair meets twice in the load phase (above) and twice more: before the filterbank (both magnitude arrays are in place;
       // each warp then takes every other pass) and after it (all partial sums of the frame are written).
       const int f = gwarp >> 1, c = gwarp & 1;
       if (f >= nfr) {
@@ -549,9 +549,12 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) frontend_kernel(const Front
         if (nb > 0) { MMB_PENDING_DIFFERENCE(); MMB_ROWS_WRITTEN(); }
       } else {
         const S* x = span0 + (int)(frame_start_sample(D->g0 + f, p.hop, N, p.origin) - D->s_begin);
-        if (WCOS) load_frame_4096_wcos<S>(lane, c, v, x, s_win, s_tw2k);
-        else load_frame_4096<S>(lane, c, v, x, s_win, s_tw2k);
+        // each warp loads half of the frame and the pair swaps the pre-stage results (frame_fft.cuh)
+        load_frame_4096_half<S, WCOS>(lane, c, v, x, s_win, s_tw2k, ex);
         frames_loaded<N, S>(p, G, r, buf, lane, GW, FPR, vid, vstride);
+        asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+        take_frame_4096_half(lane, c, v, reinterpret_cast<const float2*>(c ? pair_even : pair_odd));
+        asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");      // before pass 1 overwrites the tiles
         core_pass1(lane, v, ex, s_tw1);
         __syncwarp();
         core_pass2_load(lane, v, ex);

@@ -174,6 +174,11 @@ inline size_t widx(int off, int i, int lane) { return (size_t)off + ((size_t)(i 
 
 void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& woff, int P, FbSchedule& s) {
   const int B = cfg->num_bands;
+  // N = 4096 keeps even and odd bins in two arrays (frontend_params.h): a lane that starts at bin st reads array
+  // st & 1 at st / 2 + i and the other one beside it.  Even starts that are distinct modulo 64 put the lanes of a
+  // pass on distinct banks of both arrays (distinct starts modulo 32 do not: every load then took two wavefronts); a
+  // piece that begins at an odd bin gets one zero tap in front.
+  const bool split = cfg->frame_size == 4096 && !std::getenv("MMB_FB_SPLIT_ANY");
   s = FbSchedule();
   s.b_pad = (B + 31) & ~31;
   std::vector<Piece> rem;
@@ -189,9 +194,10 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
     }
   }
   const int dump = s.max_q * s.b_pad;                  // idle lanes write here
-  std::stable_sort(rem.begin(), rem.end(), [](const Piece& x, const Piece& y) { return x.len > y.len; });
+  auto need = [split](const Piece& x) { return x.len + (split ? (x.start & 1) : 0); };      // taps incl. a forced lead
+  std::stable_sort(rem.begin(), rem.end(), [&](const Piece& x, const Piece& y) { return need(x) > need(y); });
   while (!rem.empty()) {
-    const int T = std::min((rem[0].len + 3) & ~3, K & ~3);      // pass lengths are multiples of four
+    const int T = std::min((need(rem[0]) + 3) & ~3, K & ~3);      // pass lengths are multiples of four
     const int off = (int)s.w.size();
     const int ps = (int)s.pass.size();
     s.pass.push_back(mmb::FbPass{T, off});
@@ -205,10 +211,10 @@ void schedule_with(const mmb_config* cfg, int K, const std::vector<int32_t>& wof
       const Piece& pc = rem[i];
       bool ok = false;
       if (placed < 32) {
-        for (int lead = 0; lead <= T - pc.len && !ok; ++lead) {
+        for (int lead = split ? (pc.start & 1) : 0; lead <= T - pc.len && !ok; lead += split ? 2 : 1) {
           const int st = pc.start - lead;
           if (st < 0 || st + T > K) continue;
-          const int lane = st & 31;
+          const int lane = split ? ((st >> 1) & 31) : (st & 31);
           if (lane_used[lane]) continue;
           lane_used[lane] = true; ++placed; ok = true;
           s.start[ps * 32 + lane] = st;
